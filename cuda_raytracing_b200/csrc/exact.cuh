@@ -1,0 +1,68 @@
+// exact.cuh -- reference-exact arithmetic for the predicates that decide pixels.
+//
+// The reference's host path evaluates IEEE binary32 expressions left to right with no fused
+// multiply-add.  Everything that decides WHICH triangle a pixel reports (ray generation, the
+// world->mesh ray transform, plane hit, barycentric inside test, world-space distance) is written
+// here with __fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn/__fsqrt_rn, which nvcc never contracts, in the
+// reference's operand order.  Each helper cites the reference lines it reproduces
+// (/root/reference/CudaRaytracer/...).  Conservative culling (box tests) lives elsewhere and is free
+// to use FMA.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtb {
+
+#define XF __device__ __forceinline__
+
+XF float xm(float a, float b) { return __fmul_rn(a, b); }
+XF float xa(float a, float b) { return __fadd_rn(a, b); }
+XF float xs(float a, float b) { return __fsub_rn(a, b); }
+XF float xd(float a, float b) { return __fdiv_rn(a, b); }
+
+struct f3 { float x, y, z; };
+XF f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+
+// utils.hpp:53-55  a.x*b.x + a.y*b.y + a.z*b.z
+XF float xdot(f3 a, f3 b) { return xa(xa(xm(a.x, b.x), xm(a.y, b.y)), xm(a.z, b.z)); }
+XF f3 xsub(f3 a, f3 b) { return mk3(xs(a.x, b.x), xs(a.y, b.y), xs(a.z, b.z)); }
+XF f3 xadd(f3 a, f3 b) { return mk3(xa(a.x, b.x), xa(a.y, b.y), xa(a.z, b.z)); }
+XF f3 xscale(f3 a, float b) { return mk3(xm(a.x, b), xm(a.y, b), xm(a.z, b)); }
+XF f3 xmul3(f3 a, f3 b) { return mk3(xm(a.x, b.x), xm(a.y, b.y), xm(a.z, b.z)); }
+// utils.hpp:49-51
+XF f3 xcross(f3 a, f3 b)
+{
+    return mk3(xs(xm(a.y, b.z), xm(a.z, b.y)), xs(xm(a.z, b.x), xm(a.x, b.z)), xs(xm(a.x, b.y), xm(a.y, b.x)));
+}
+
+// utils.hpp:12-27, `long` read as 32 bits
+XF float q_rsqrt(float number)
+{
+    float x2 = xm(number, 0.5f);
+    int i = __float_as_int(number);
+    i = 0x5f3759df - (i >> 1);
+    float y = __int_as_float(i);
+    return xm(y, xs(1.5f, xm(xm(x2, y), y)));
+}
+// utils.hpp:37-47
+XF f3 xnormalize(f3 v)
+{
+    float inv = q_rsqrt(xa(xa(xm(v.x, v.x), xm(v.y, v.y)), xm(v.z, v.z)));
+    return mk3(xm(v.x, inv), xm(v.y, inv), xm(v.z, inv));
+}
+// utils.hpp:29-31
+XF float xmagnitude(f3 v) { return __fsqrt_rn(xa(xa(xm(v.x, v.x), xm(v.y, v.y)), xm(v.z, v.z))); }
+
+// transforms.hpp:165-176 apply_quat
+XF f3 xapply_quat(float4 q, f3 v)
+{
+    float a = xs(xs(xm(-v.x, q.y), xm(v.y, q.z)), xm(v.z, q.w));
+    float b = xs(xa(xm(v.x, q.x), xm(v.y, q.w)), xm(v.z, q.z));
+    float c = xs(xa(xm(v.y, q.x), xm(v.z, q.y)), xm(v.x, q.w));
+    float d = xs(xa(xm(v.z, q.x), xm(v.x, q.z)), xm(v.y, q.y));
+    return mk3(xa(xs(xs(xm(q.x, b), xm(q.y, a)), xm(q.z, d)), xm(q.w, c)),
+               xa(xs(xs(xm(q.x, c), xm(q.z, a)), xm(q.w, b)), xm(q.y, d)),
+               xa(xs(xs(xm(q.x, d), xm(q.w, a)), xm(q.y, c)), xm(q.z, b)));
+}
+
+}  // namespace rtb

@@ -1,0 +1,486 @@
+// rtb_api.cu -- the C-ABI (include/rtb200.h): context, BLAS/TLAS management, scene upload, render.
+// Host code only orchestrates; every pixel and every tree node is produced by the CUDA kernels in
+// rtb_build.cu / rtb_render.cu.  There is no CPU fallback anywhere in this library.
+#include "rtb_build.cuh"
+#include "rtb_render.cuh"
+#include "rtb_hostmath.h"
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+using namespace rtb;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static int cuda_fail(cudaError_t e, const char* where)
+{
+    g_err = std::string(where) + ": " + cudaGetErrorString(e);
+    return RTB_ERR_CUDA;
+}
+#define CU(x, where) do { cudaError_t _e = (x); if (_e != cudaSuccess) return cuda_fail(_e, where); } while (0)
+
+struct MeshRec {
+    bool alive = false;
+    int n = 0;
+    float4* tri_rec = nullptr; float2* uvs = nullptr;
+    int tri_cap = 0;
+    BvhResult bvh;
+    rtb_mesh_info info{};
+};
+
+struct rtb_context {
+    int device = 0;
+    std::vector<MeshRec> meshes;
+    std::vector<rtb_material> materials_h;
+    std::vector<rtb_instance> instances_h;
+    rtb_material* materials_d = nullptr; int materials_cap = 0;
+    float4* inst_d = nullptr; int inst_cap = 0;
+    MeshDev* meshes_d = nullptr; int meshes_cap = 0;
+    bool mesh_table_dirty = true;
+    BvhResult tlas;
+    float4* ibox_min = nullptr; float4* ibox_max = nullptr; int ibox_cap = 0;
+    Counters* counters_d = nullptr;
+    Arena ws;                      // build workspace (grow-only)
+    Arena stage;                   // triangle upload staging + prim boxes
+    std::vector<unsigned char*> textures;
+    // internal frame for rtb_render_host
+    unsigned char* frame_d = nullptr; size_t frame_pitch = 0; int frame_w = 0, frame_h = 0;
+    int32_t* aov_prim_d = nullptr; int32_t* aov_inst_d = nullptr; float* aov_t_d = nullptr; size_t aov_cap = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+    int opt_counters = 0, opt_leaf = 4, opt_key_bits = 0;
+    void* wf = nullptr;            // wavefront state (rtb_wavefront.cu)
+};
+
+extern "C" {
+
+const char* rtb_last_error(void) { return g_err.c_str(); }
+int rtb_version(void) { return 100; }
+
+int rtb_context_create(int device, rtb_context** out)
+{
+    if (!out) return fail(RTB_ERR_INVALID, "rtb_context_create: out is NULL");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0 || device < 0 || device >= count)
+        return fail(RTB_ERR_NO_DEVICE, std::string("rtb_context_create: no usable CUDA device (") +
+                                           (e != cudaSuccess ? cudaGetErrorString(e) : "index out of range") + "); there is no CPU fallback");
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+    if (prop.major != 10)
+        return fail(RTB_ERR_NO_DEVICE, "rtb_context_create: device is not sm_100 (kernels are built for sm_100a only)");
+    CU(cudaSetDevice(device), "cudaSetDevice");
+    rtb_context* c = new rtb_context();
+    c->device = device;
+    CU(cudaMalloc((void**)&c->counters_d, sizeof(Counters)), "cudaMalloc counters");
+    CU(cudaMemset(c->counters_d, 0, sizeof(Counters)), "cudaMemset counters");
+    CU(cudaEventCreate(&c->ev0), "cudaEventCreate");
+    CU(cudaEventCreate(&c->ev1), "cudaEventCreate");
+    *out = c;
+    return RTB_OK;
+}
+
+static void free_mesh(MeshRec& m)
+{
+    if (m.tri_rec) cudaFree(m.tri_rec);
+    if (m.uvs) cudaFree(m.uvs);
+    if (m.bvh.nodes) cudaFree(m.bvh.nodes);
+    if (m.bvh.order) cudaFree(m.bvh.order);
+    m = MeshRec();
+}
+
+void rtb_wavefront_release(rtb_context* c);
+
+void rtb_context_destroy(rtb_context* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (auto& m : c->meshes) if (m.alive) free_mesh(m);
+    for (auto* t : c->textures) cudaFree(t);
+    if (c->materials_d) cudaFree(c->materials_d);
+    if (c->inst_d) cudaFree(c->inst_d);
+    if (c->meshes_d) cudaFree(c->meshes_d);
+    if (c->tlas.nodes) cudaFree(c->tlas.nodes);
+    if (c->tlas.order) cudaFree(c->tlas.order);
+    if (c->ibox_min) cudaFree(c->ibox_min);
+    if (c->ibox_max) cudaFree(c->ibox_max);
+    if (c->counters_d) cudaFree(c->counters_d);
+    if (c->frame_d) cudaFree(c->frame_d);
+    if (c->aov_prim_d) cudaFree(c->aov_prim_d);
+    if (c->aov_inst_d) cudaFree(c->aov_inst_d);
+    if (c->aov_t_d) cudaFree(c->aov_t_d);
+    rtb_wavefront_release(c);
+    c->ws.release(); c->stage.release();
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    delete c;
+}
+
+int rtb_set_option(rtb_context* c, const char* name, int value)
+{
+    if (!c || !name) return fail(RTB_ERR_INVALID, "rtb_set_option: NULL argument");
+    std::string n(name);
+    if (n == "counters") c->opt_counters = value;
+    else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
+    else if (n == "key_bits") c->opt_key_bits = value;
+    else return fail(RTB_ERR_INVALID, "rtb_set_option: unknown option " + n);
+    return RTB_OK;
+}
+
+// ------------------------------------------------------------------ BLAS
+static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int n, int on_device)
+{
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    cudaStream_t st = 0;
+    const size_t nn = (size_t)(n > 0 ? n : 1);
+    c->stage.reset();
+    CU(c->stage.reserve(nn * (on_device ? 32 : 32 + sizeof(rtb_triangle)) + 4096), "stage reserve");
+    float4* bmin = c->stage.take<float4>(nn);
+    float4* bmax = c->stage.take<float4>(nn);
+    const rtb_triangle* tris_d = tris;
+    if (!on_device) {
+        rtb_triangle* up = c->stage.take<rtb_triangle>(nn);
+        if (n > 0) CU(cudaMemcpyAsync(up, tris, sizeof(rtb_triangle) * (size_t)n, cudaMemcpyHostToDevice, st), "upload triangles");
+        tris_d = up;
+    }
+    if (m.tri_cap < n || !m.tri_rec) {
+        if (m.tri_rec) cudaFree(m.tri_rec);
+        if (m.uvs) cudaFree(m.uvs);
+        m.tri_rec = nullptr; m.uvs = nullptr;
+        CU(cudaMalloc((void**)&m.tri_rec, sizeof(float4) * TRI_F4 * nn), "cudaMalloc triangle records");
+        CU(cudaMalloc((void**)&m.uvs, sizeof(float2) * 3 * nn), "cudaMalloc uvs");
+        m.tri_cap = (int)nn;
+    }
+    CU(cudaEventRecord(c->ev0, st), "event");
+    CU(mesh_prim_boxes(tris_d, n, bmin, bmax, st), "k_tri_boxes");
+    int key_bits = c->opt_key_bits ? c->opt_key_bits : (n > (1 << 21) ? 64 : 32);
+    CU(build_bvh(bmin, bmax, n, c->opt_leaf, key_bits, m.bvh, c->ws, st), "build_bvh");
+    CU(mesh_emit(tris_d, n, m.bvh.order, m.tri_rec, m.uvs, st), "k_emit_tris");
+    CU(cudaEventRecord(c->ev1, st), "event");
+    CU(cudaEventSynchronize(c->ev1), "build sync");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    m.n = n; m.alive = true;
+    rtb_mesh_info& I = m.info;
+    I.num_triangles = n; I.num_nodes = m.bvh.num_nodes; I.num_leaves = m.bvh.num_leaves; I.max_leaf_size = m.bvh.max_leaf;
+    I.depth = m.bvh.depth; I.stack_need = 3 * m.bvh.depth + 2; I.build_ms = ms; I.sah_cost = m.bvh.sah;
+    for (int k = 0; k < 3; k++) { I.bounds_min[k] = m.bvh.bounds[k]; I.bounds_max[k] = m.bvh.bounds[k + 3]; }
+    I.device_bytes = sizeof(float4) * TRI_F4 * nn + sizeof(float2) * 3 * nn + sizeof(float4) * NODE_F4 * (size_t)m.bvh.node_cap +
+                     sizeof(unsigned) * (size_t)m.bvh.order_cap;
+    c->mesh_table_dirty = true;
+    return RTB_OK;
+}
+
+int rtb_mesh_create(rtb_context* c, const rtb_triangle* tris, int n, int on_device, int* mesh_id)
+{
+    if (!c || n < 0 || (n > 0 && !tris) || !mesh_id) return fail(RTB_ERR_INVALID, "rtb_mesh_create: bad argument");
+    c->meshes.emplace_back();
+    int rc = build_mesh(c, c->meshes.back(), tris, n, on_device);
+    if (rc != RTB_OK) { c->meshes.pop_back(); return rc; }
+    *mesh_id = (int)c->meshes.size() - 1;
+    return RTB_OK;
+}
+
+int rtb_mesh_rebuild(rtb_context* c, int id, const rtb_triangle* tris, int n, int on_device)
+{
+    if (!c || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive || n < 0 || (n > 0 && !tris))
+        return fail(RTB_ERR_INVALID, "rtb_mesh_rebuild: bad argument");
+    return build_mesh(c, c->meshes[id], tris, n, on_device);
+}
+
+int rtb_mesh_info_get(rtb_context* c, int id, rtb_mesh_info* out)
+{
+    if (!c || !out || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive)
+        return fail(RTB_ERR_INVALID, "rtb_mesh_info_get: bad argument");
+    *out = c->meshes[id].info;
+    return RTB_OK;
+}
+
+int rtb_mesh_destroy(rtb_context* c, int id)
+{
+    if (!c || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive) return fail(RTB_ERR_INVALID, "rtb_mesh_destroy: bad argument");
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_mesh(c->meshes[id]);
+    c->mesh_table_dirty = true;
+    return RTB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ scene
+namespace rtb { cudaError_t launch_wavefront(rtb_context* c, void** wf_state, const SceneDev& sc, const FrameParams& P, unsigned char* img,
+                                             size_t pitch, const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st); }
+
+extern "C" {
+
+int rtb_texture_upload(rtb_context* c, const unsigned char* bgr, int w, int h, unsigned char** dev, size_t* pitch)
+{
+    if (!c || !bgr || w <= 0 || h <= 0 || !dev || !pitch) return fail(RTB_ERR_INVALID, "rtb_texture_upload: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    unsigned char* d = nullptr;
+    CU(cudaMallocPitch((void**)&d, pitch, (size_t)w * 3, (size_t)h), "cudaMallocPitch texture");   // as Material.hpp:37
+    CU(cudaMemcpy2D(d, *pitch, bgr, (size_t)w * 3, (size_t)w * 3, (size_t)h, cudaMemcpyHostToDevice), "texture upload");
+    c->textures.push_back(d);
+    *dev = d;
+    return RTB_OK;
+}
+
+int rtb_set_materials(rtb_context* c, const rtb_material* mats, int n)
+{
+    if (!c || n < 0 || (n > 0 && !mats)) return fail(RTB_ERR_INVALID, "rtb_set_materials: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    c->materials_h.assign(mats, mats + n);
+    if (c->materials_cap < n || !c->materials_d) {
+        if (c->materials_d) cudaFree(c->materials_d);
+        c->materials_d = nullptr;
+        CU(cudaMalloc((void**)&c->materials_d, sizeof(rtb_material) * (size_t)std::max(n, 1)), "cudaMalloc materials");
+        c->materials_cap = std::max(n, 1);
+    }
+    if (n > 0) CU(cudaMemcpy(c->materials_d, mats, sizeof(rtb_material) * (size_t)n, cudaMemcpyHostToDevice), "materials upload");
+    return RTB_OK;
+}
+
+// instance record (see rtb_internal.cuh) + conservative world box
+static int pack_instance(rtb_context* c, const rtb_instance& in, float4 rec[INST_F4], float lo[3], float hi[3])
+{
+    if (in.mesh_index < 0 || in.mesh_index >= (int)c->meshes.size() || !c->meshes[in.mesh_index].alive)
+        return fail(RTB_ERR_INVALID, "instance refers to a mesh that does not exist");
+    if (in.material_index < 0 || in.material_index >= (int)c->materials_h.size())
+        return fail(RTB_ERR_INVALID, "instance refers to a material that does not exist (call rtb_set_materials first)");
+    hm::Quat qp = hm::euler_to_quat(in.rotation[0], in.rotation[1], in.rotation[2]);             // raycast.cu:33
+    hm::Quat qi = hm::euler_to_quat(in.inv_rotation[0], in.inv_rotation[1], in.inv_rotation[2]); // raycast.cu:115
+    // apply_lre(pose, .) rotates by pose.yaw/pitch/roll (transforms.hpp:223-226); MeshInstance::build_inv makes
+    // rotation == pose angles, but a caller may have filled the record by hand, so honour each field separately.
+    hm::Quat qpl = hm::euler_to_quat(in.pose.yaw, in.pose.pitch, in.pose.roll);
+    hm::Quat qil = hm::euler_to_quat(in.inv_pose.yaw, in.inv_pose.pitch, in.inv_pose.roll);
+    if (memcmp(&qp, &qpl, sizeof qp) != 0 || memcmp(&qi, &qil, sizeof qi) != 0)
+        return fail(RTB_ERR_INVALID, "instance rotation/inv_rotation differ from pose/inv_pose angles (call build_inv)");
+    auto asf = [](int i) { float f; memcpy(&f, &i, 4); return f; };
+    rec[0] = make_float4(qp.x, qp.y, qp.z, qp.w);
+    rec[1] = make_float4(in.pose.x, in.pose.y, in.pose.z, asf(in.mesh_index));
+    rec[2] = make_float4(in.inv_scale[0], in.inv_scale[1], in.inv_scale[2], asf(in.material_index));
+    rec[3] = make_float4(qi.x, qi.y, qi.z, qi.w);
+    rec[4] = make_float4(in.inv_pose.x, in.inv_pose.y, in.inv_pose.z, 0.f);
+    rec[5] = make_float4(in.scale[0], in.scale[1], in.scale[2], 0.f);
+    // world box: the ray enters mesh space as m = (R (w - t)) * inv_scale, so w = R^T (m / inv_scale) + t.  Double
+    // precision + padding: the box only culls, it must merely contain every world point the forward map sends inside.
+    const rtb_mesh_info& mi = c->meshes[in.mesh_index].info;
+    float Rf[3][3];
+    hm::euler_to_matrix(in.pose.yaw, in.pose.pitch, in.pose.roll, Rf);
+    double wlo[3] = { 1e300, 1e300, 1e300 }, whi[3] = { -1e300, -1e300, -1e300 };
+    double mag = 0;
+    for (int k = 0; k < 8; k++) {
+        double m[3];
+        for (int a = 0; a < 3; a++) {
+            double v = ((k >> a) & 1) ? mi.bounds_max[a] : mi.bounds_min[a];
+            m[a] = v / (double)in.inv_scale[a];
+        }
+        for (int a = 0; a < 3; a++) {
+            double w = Rf[0][a] * m[0] + Rf[1][a] * m[1] + Rf[2][a] * m[2] + (&in.pose.x)[a];
+            wlo[a] = std::min(wlo[a], w); whi[a] = std::max(whi[a], w);
+            mag = std::max(mag, std::fabs(w));
+        }
+    }
+    if (mi.num_triangles == 0) { for (int a = 0; a < 3; a++) { wlo[a] = 1e30; whi[a] = -1e30; } mag = 0; }
+    const double pad = 1e-4 * mag + 1e-5;
+    for (int a = 0; a < 3; a++) { lo[a] = (float)(wlo[a] - pad); hi[a] = (float)(whi[a] + pad); }
+    return RTB_OK;
+}
+
+static int rebuild_tlas(rtb_context* c)
+{
+    const int n = (int)c->instances_h.size();
+    const int cap = std::max(n, 1);
+    if (c->inst_cap < cap) {
+        if (c->inst_d) cudaFree(c->inst_d);
+        if (c->ibox_min) cudaFree(c->ibox_min);
+        if (c->ibox_max) cudaFree(c->ibox_max);
+        c->inst_d = c->ibox_min = c->ibox_max = nullptr;
+        CU(cudaMalloc((void**)&c->inst_d, sizeof(float4) * INST_F4 * (size_t)cap), "cudaMalloc instances");
+        CU(cudaMalloc((void**)&c->ibox_min, sizeof(float4) * (size_t)cap), "cudaMalloc instance boxes");
+        CU(cudaMalloc((void**)&c->ibox_max, sizeof(float4) * (size_t)cap), "cudaMalloc instance boxes");
+        c->inst_cap = cap;
+    }
+    std::vector<float4> rec((size_t)cap * INST_F4), lo(cap), hi(cap);
+    for (int i = 0; i < n; i++) {
+        float l[3], h[3];
+        int rc = pack_instance(c, c->instances_h[i], &rec[(size_t)i * INST_F4], l, h);
+        if (rc != RTB_OK) return rc;
+        lo[i] = make_float4(l[0], l[1], l[2], 0.f); hi[i] = make_float4(h[0], h[1], h[2], 0.f);
+    }
+    if (n > 0) {
+        CU(cudaMemcpy(c->inst_d, rec.data(), sizeof(float4) * INST_F4 * (size_t)n, cudaMemcpyHostToDevice), "instances upload");
+        CU(cudaMemcpy(c->ibox_min, lo.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
+        CU(cudaMemcpy(c->ibox_max, hi.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
+    }
+    CU(build_bvh(c->ibox_min, c->ibox_max, n, 1, 32, c->tlas, c->ws, 0), "build TLAS");
+    return RTB_OK;
+}
+
+int rtb_set_instances(rtb_context* c, const rtb_instance* insts, int n)
+{
+    if (!c || n < 0 || (n > 0 && !insts)) return fail(RTB_ERR_INVALID, "rtb_set_instances: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    c->instances_h.assign(insts, insts + n);
+    return rebuild_tlas(c);
+}
+
+int rtb_update_instance(rtb_context* c, int index, const rtb_instance* inst)
+{
+    if (!c || !inst || index < 0 || index >= (int)c->instances_h.size()) return fail(RTB_ERR_INVALID, "rtb_update_instance: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    c->instances_h[index] = *inst;
+    return rebuild_tlas(c);
+}
+
+// ------------------------------------------------------------------ render
+static int make_scene(rtb_context* c, SceneDev& sc)
+{
+    if (!c->tlas.nodes) return fail(RTB_ERR_STATE, "render: no instances set (call rtb_set_instances)");
+    if (c->mesh_table_dirty) {
+        const int n = (int)c->meshes.size(), cap = std::max(n, 1);
+        if (c->meshes_cap < cap) {
+            if (c->meshes_d) cudaFree(c->meshes_d);
+            c->meshes_d = nullptr;
+            CU(cudaMalloc((void**)&c->meshes_d, sizeof(MeshDev) * (size_t)cap), "cudaMalloc mesh table");
+            c->meshes_cap = cap;
+        }
+        std::vector<MeshDev> t(cap);
+        for (int i = 0; i < n; i++) {
+            const MeshRec& m = c->meshes[i];
+            t[i].nodes = m.bvh.nodes; t[i].tris = m.tri_rec; t[i].uvs = m.uvs; t[i].num_triangles = m.n; t[i].pad = 0;
+        }
+        CU(cudaMemcpy(c->meshes_d, t.data(), sizeof(MeshDev) * (size_t)cap, cudaMemcpyHostToDevice), "mesh table upload");
+        c->mesh_table_dirty = false;
+    }
+    for (const auto& in : c->instances_h)
+        if (!c->meshes[in.mesh_index].alive) return fail(RTB_ERR_STATE, "render: an instance refers to a destroyed mesh");
+    sc.tlas_nodes = c->tlas.nodes; sc.tlas_index = (const int*)c->tlas.order; sc.inst = c->inst_d; sc.meshes = c->meshes_d;
+    sc.materials = c->materials_d; sc.num_instances = (int)c->instances_h.size(); sc.num_materials = (int)c->materials_h.size();
+    return RTB_OK;
+}
+
+static int make_frame(const rtb_render_params* p, FrameParams& P)
+{
+    if (p->width <= 0 || p->height <= 0) return fail(RTB_ERR_INVALID, "render: width/height must be positive");
+    if (p->mode < RTB_MODE_REFERENCE || p->mode > RTB_MODE_PATH) return fail(RTB_ERR_INVALID, "render: unknown mode");
+    P.width = p->width; P.height = p->height;
+    memcpy(P.K_inv, p->K_inv, sizeof P.K_inv); memcpy(P.D, p->D, sizeof P.D);
+    P.ox = p->pose.x; P.oy = p->pose.y; P.oz = p->pose.z;
+    hm::Quat q = hm::euler_to_quat(p->inv_pose.yaw, p->inv_pose.pitch, p->inv_pose.roll);       // raycast.cu:185
+    P.q_cam = make_float4(q.x, q.y, q.z, q.w);
+    P.mode = p->mode; P.max_depth = std::max(0, p->max_depth); P.spp = std::max(1, p->spp); P.seed = p->seed;
+    P.tile_count = std::max(1, p->tile_count); P.tile_rank = p->tile_rank;
+    if (P.tile_rank < 0 || P.tile_rank >= P.tile_count) return fail(RTB_ERR_INVALID, "render: tile_rank out of range");
+    hm::V3 L = hm::normalize(hm::V3{ (float)-0.2, 0.0f, 1.0f });                                 // raycast.cu:249-250
+    P.light_dir = make_float3(L.x, L.y, L.z);
+    return RTB_OK;
+}
+
+static int render_impl(rtb_context* c, const rtb_render_params* p, unsigned char* img, size_t pitch, const rtb_aovs* aovs, cudaStream_t st)
+{
+    SceneDev sc; FrameParams P;
+    int rc = make_scene(c, sc); if (rc != RTB_OK) return rc;
+    rc = make_frame(p, P); if (rc != RTB_OK) return rc;
+    if (pitch < (size_t)p->width * 3) return fail(RTB_ERR_INVALID, "render: pitch smaller than a row");
+    rtb_aovs a = { nullptr, nullptr, nullptr };
+    if (aovs) a = *aovs;
+    CU(cudaMemsetAsync(c->counters_d, 0, sizeof(Counters), st), "counters reset");
+    if (p->mode == RTB_MODE_REFERENCE || p->mode == RTB_MODE_SHADOW)
+        CU(launch_render(sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "render launch");
+    else
+        CU(launch_wavefront(c, &c->wf, sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "wavefront launch");
+    return RTB_OK;
+}
+
+int rtb_render(rtb_context* c, const rtb_render_params* p, unsigned char* img, size_t pitch, const rtb_aovs* aovs, void* stream)
+{
+    if (!c || !p || !img) return fail(RTB_ERR_INVALID, "rtb_render: NULL argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    return render_impl(c, p, img, pitch, aovs, (cudaStream_t)stream);
+}
+
+int rtb_render_host(rtb_context* c, const rtb_render_params* p, unsigned char* img_host, size_t pitch_host, const rtb_aovs* aovs_host)
+{
+    if (!c || !p || !img_host) return fail(RTB_ERR_INVALID, "rtb_render_host: NULL argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    if (p->width <= 0 || p->height <= 0) return fail(RTB_ERR_INVALID, "render: width/height must be positive");
+    if (pitch_host < (size_t)p->width * 3) return fail(RTB_ERR_INVALID, "render: pitch smaller than a row");
+    if (c->frame_w != p->width || c->frame_h != p->height) {
+        if (c->frame_d) cudaFree(c->frame_d);
+        c->frame_d = nullptr; c->frame_w = c->frame_h = 0;
+        CU(cudaMallocPitch((void**)&c->frame_d, &c->frame_pitch, (size_t)p->width * 3, (size_t)p->height), "cudaMallocPitch frame");
+        c->frame_w = p->width; c->frame_h = p->height;
+    }
+    const size_t npx = (size_t)p->width * p->height;
+    rtb_aovs dev = { nullptr, nullptr, nullptr };
+    if (aovs_host && (aovs_host->prim || aovs_host->inst || aovs_host->t)) {
+        if (c->aov_cap < npx) {
+            if (c->aov_prim_d) cudaFree(c->aov_prim_d);
+            if (c->aov_inst_d) cudaFree(c->aov_inst_d);
+            if (c->aov_t_d) cudaFree(c->aov_t_d);
+            c->aov_prim_d = c->aov_inst_d = nullptr; c->aov_t_d = nullptr; c->aov_cap = 0;
+            CU(cudaMalloc((void**)&c->aov_prim_d, 4 * npx), "cudaMalloc aov");
+            CU(cudaMalloc((void**)&c->aov_inst_d, 4 * npx), "cudaMalloc aov");
+            CU(cudaMalloc((void**)&c->aov_t_d, 4 * npx), "cudaMalloc aov");
+            c->aov_cap = npx;
+        }
+        dev.prim = c->aov_prim_d; dev.inst = c->aov_inst_d; dev.t = c->aov_t_d;
+    }
+    cudaStream_t st = 0;
+    CU(cudaEventRecord(c->ev0, st), "event");
+    int rc = render_impl(c, p, c->frame_d, c->frame_pitch, &dev, st);
+    if (rc != RTB_OK) return rc;
+    CU(cudaEventRecord(c->ev1, st), "event");
+    // only the rows this rank rendered are meaningful when tile_count > 1; copy the whole frame anyway
+    CU(cudaMemcpy2DAsync(img_host, pitch_host, c->frame_d, c->frame_pitch, (size_t)p->width * 3, (size_t)p->height, cudaMemcpyDeviceToHost, st), "frame download");
+    if (dev.prim) {
+        if (aovs_host->prim) CU(cudaMemcpyAsync(aovs_host->prim, dev.prim, 4 * npx, cudaMemcpyDeviceToHost, st), "aov download");
+        if (aovs_host->inst) CU(cudaMemcpyAsync(aovs_host->inst, dev.inst, 4 * npx, cudaMemcpyDeviceToHost, st), "aov download");
+        if (aovs_host->t) CU(cudaMemcpyAsync(aovs_host->t, dev.t, 4 * npx, cudaMemcpyDeviceToHost, st), "aov download");
+    }
+    CU(cudaStreamSynchronize(st), "render sync");
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    Counters h;
+    CU(cudaMemcpy(&h, c->counters_d, sizeof h, cudaMemcpyDeviceToHost), "counters");
+    if (h.overflow) return fail(RTB_ERR_OVERFLOW, "render: traversal stack / ray queue overflow (result discarded)");
+    return RTB_OK;
+}
+
+int rtb_synchronize(rtb_context* c)
+{
+    if (!c) return fail(RTB_ERR_INVALID, "rtb_synchronize: NULL context");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    CU(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
+    return RTB_OK;
+}
+
+int rtb_frame_stats_get(rtb_context* c, rtb_frame_stats* out)
+{
+    if (!c || !out) return fail(RTB_ERR_INVALID, "rtb_frame_stats_get: NULL argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    Counters h;
+    CU(cudaMemcpy(&h, c->counters_d, sizeof h, cudaMemcpyDeviceToHost), "counters");
+    out->rays = h.rays; out->nodes_visited = h.nodes; out->tris_tested = h.tris; out->device_ms = c->last_ms; out->overflow = h.overflow;
+    if (h.overflow) return fail(RTB_ERR_OVERFLOW, "render: traversal stack / ray queue overflow");
+    return RTB_OK;
+}
+
+// ------------------------------------------------------------------ host helpers
+void rtb_invert_intrinsic(const float K[9], float Ki[9]) { hm::invert_intrinsic(K, Ki); }
+void rtb_invert_lre(const rtb_lre* in, rtb_lre* out) { *out = hm::invert_pose(*in); }
+void rtb_instance_build_inv(rtb_instance* inst) { hm::instance_build_inv(*inst); }
+void rtb_triangle_init(rtb_triangle* t, const float a[3], const float b[3], const float c[3])
+{
+    memset(t, 0, sizeof *t);
+    for (int k = 0; k < 3; k++) { t->vertices[0][k] = a[k]; t->vertices[1][k] = b[k]; t->vertices[2][k] = c[k]; }
+    hm::V3 n = hm::face_normal(hm::V3{ a[0], a[1], a[2] }, hm::V3{ b[0], b[1], b[2] }, hm::V3{ c[0], c[1], c[2] });
+    t->normal[0] = n.x; t->normal[1] = n.y; t->normal[2] = n.z;
+}
+void rtb_free(void* p) { free(p); }
+
+}  // extern "C"

@@ -1,0 +1,424 @@
+// rtb_build.cu -- on-device LBVH builder for sm_100a.
+//
+// Replaces the reference's single-threaded recursive host builder (BVHTree::fill, BVHTree.hpp:203-292,
+// 15 re-scans per node) and its one-cudaMalloc-per-leaf upload (BVHTree.hpp:97-114,364-383):
+//   prim boxes -> scene bounds -> Morton keys -> radix sort -> Karras 2012 radix tree -> bottom-up
+//   AABB fit + SAH leaf decision -> top-down collapse to 128-byte BVH4 nodes -> triangle records.
+// The tree only culls (rtb_trace.cuh keeps the reference's hit predicate), so it is free to differ
+// from the reference's tree.  All stages are HBM-bound streaming kernels.
+#include "rtb_build.cuh"
+#include "rtb_sort.cuh"
+#include <cstdio>
+
+namespace rtb {
+
+// ------------------------------------------------------------------ arena
+cudaError_t Arena::reserve(size_t bytes)
+{
+    if (bytes <= cap) return cudaSuccess;
+    if (base) cudaFree(base);
+    base = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc((void**)&base, bytes);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+}
+void Arena::release()
+{
+    if (base) cudaFree(base);
+    base = nullptr; cap = used = 0;
+}
+
+// ------------------------------------------------------------------ helpers
+__device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+struct BuildCounters {
+    int bounds[6];          // ordered-int encoded scene bounds (min xyz, max xyz)
+    int cbounds[6];         // centroid bounds
+    int n_wide;             // wide nodes allocated
+    int n_leaves, max_leaf, max_level;
+    float sah;
+    int qcount[72];         // collapse work-queue sizes per level
+};
+
+// ------------------------------------------------------------------ 1. primitive boxes
+// Reads the reference's 72-byte AoS triangles (TrianglePrimitive.hpp:8-11); bounds as BVHTree::grow_to_include (175-190).
+__global__ void k_tri_boxes(const rtb_triangle* __restrict__ tris, int n, float4* __restrict__ bmin, float4* __restrict__ bmax)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* v = (const float*)(tris + i);
+    float x0 = v[0], y0 = v[1], z0 = v[2], x1 = v[3], y1 = v[4], z1 = v[5], x2 = v[6], y2 = v[7], z2 = v[8];
+    bmin[i] = make_float4(fminf(fminf(x0, x1), x2), fminf(fminf(y0, y1), y2), fminf(fminf(z0, z1), z2), 0.f);
+    bmax[i] = make_float4(fmaxf(fmaxf(x0, x1), x2), fmaxf(fmaxf(y0, y1), y2), fmaxf(fmaxf(z0, z1), z2), 0.f);
+}
+
+__global__ void k_init_counters(BuildCounters* c)
+{
+    int t = threadIdx.x;
+    if (t < 3) { c->bounds[t] = f2ord(FLT_MAX); c->bounds[t + 3] = f2ord(-FLT_MAX); c->cbounds[t] = f2ord(FLT_MAX); c->cbounds[t + 3] = f2ord(-FLT_MAX); }
+    if (t == 0) { c->n_wide = 1; c->n_leaves = 0; c->max_leaf = 0; c->max_level = 0; c->sah = 0.f; }
+    if (t < 72) c->qcount[t] = 0;
+}
+
+__global__ void __launch_bounds__(256) k_scene_bounds(const float4* __restrict__ bmin, const float4* __restrict__ bmax, int n, BuildCounters* c)
+{
+    float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    float clo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, chi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float4 a = bmin[i], b = bmax[i];
+        float av[3] = { a.x, a.y, a.z }, bv[3] = { b.x, b.y, b.z };
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            lo[k] = fminf(lo[k], av[k]); hi[k] = fmaxf(hi[k], bv[k]);
+            float cc = 0.5f * (av[k] + bv[k]);
+            clo[k] = fminf(clo[k], cc); chi[k] = fmaxf(chi[k], cc);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+            clo[k] = fminf(clo[k], __shfl_xor_sync(0xffffffffu, clo[k], o));
+            chi[k] = fmaxf(chi[k], __shfl_xor_sync(0xffffffffu, chi[k], o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicMin(&c->bounds[k], f2ord(lo[k])); atomicMax(&c->bounds[k + 3], f2ord(hi[k]));
+            atomicMin(&c->cbounds[k], f2ord(clo[k])); atomicMax(&c->cbounds[k + 3], f2ord(chi[k]));
+        }
+    }
+}
+
+// ------------------------------------------------------------------ 2. Morton keys
+__device__ __forceinline__ unsigned expand10(unsigned v)
+{
+    v = (v * 0x00010001u) & 0xFF0000FFu; v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u; v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+__device__ __forceinline__ unsigned long long expand21(unsigned long long v)
+{
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x1f00000000ffffull; v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full; v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+template <typename K>
+__global__ void k_morton(const float4* __restrict__ bmin, const float4* __restrict__ bmax, int n, const BuildCounters* __restrict__ c,
+                         K* __restrict__ keys, unsigned* __restrict__ vals)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = bmin[i], b = bmax[i];
+    float cx = 0.5f * (a.x + b.x), cy = 0.5f * (a.y + b.y), cz = 0.5f * (a.z + b.z);
+    float lx = ord2f(c->cbounds[0]), ly = ord2f(c->cbounds[1]), lz = ord2f(c->cbounds[2]);
+    float ex = ord2f(c->cbounds[3]) - lx, ey = ord2f(c->cbounds[4]) - ly, ez = ord2f(c->cbounds[5]) - lz;
+    float nx = ex > 0.f ? (cx - lx) / ex : 0.f, ny = ey > 0.f ? (cy - ly) / ey : 0.f, nz = ez > 0.f ? (cz - lz) / ez : 0.f;
+    if (sizeof(K) == 4) {
+        unsigned ix = min(1023u, (unsigned)(nx * 1024.f)), iy = min(1023u, (unsigned)(ny * 1024.f)), iz = min(1023u, (unsigned)(nz * 1024.f));
+        keys[i] = (K)((expand10(ix) << 2) | (expand10(iy) << 1) | expand10(iz));
+    } else {
+        unsigned long long ix = min(2097151u, (unsigned)(nx * 2097152.f)), iy = min(2097151u, (unsigned)(ny * 2097152.f)),
+                           iz = min(2097151u, (unsigned)(nz * 2097152.f));
+        keys[i] = (K)((expand21(ix) << 2) | (expand21(iy) << 1) | expand21(iz));
+    }
+    vals[i] = (unsigned)i;
+}
+
+// ------------------------------------------------------------------ 3. Karras 2012 radix tree
+// node ids: internal 0..n-2, leaf j -> n-1+j.
+template <typename K>
+__device__ __forceinline__ int delta(const K* __restrict__ keys, int n, int i, int j)
+{
+    if (j < 0 || j >= n) return -1;
+    K a = keys[i], b = keys[j];
+    if (a == b) return (int)(sizeof(K) * 8) + __clz(i ^ j);
+    return sizeof(K) == 4 ? __clz((unsigned)(a ^ b)) : __clzll((long long)(a ^ b));
+}
+
+template <typename K>
+__global__ void k_hierarchy(const K* __restrict__ keys, int n, int* __restrict__ left, int* __restrict__ right,
+                            int* __restrict__ parent, int2* __restrict__ range)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    int lc = lo == gamma ? (n - 1 + gamma) : gamma;
+    int rc = hi == gamma + 1 ? (n - 1 + gamma + 1) : gamma + 1;
+    left[i] = lc; right[i] = rc;
+    parent[lc] = i; parent[rc] = i;
+    range[i] = make_int2(lo, hi);
+    if (i == 0) parent[0] = -1;
+}
+
+// ------------------------------------------------------------------ 4. bottom-up fit + SAH leaf decision
+// nb_min[id].w = half surface area, nb_max[id].w = SAH cost of the subtree; flags[id]=1: emit subtree as one leaf.
+__device__ __forceinline__ float half_area(float4 a, float4 b)
+{
+    float x = b.x - a.x, y = b.y - a.y, z = b.z - a.z;
+    return x * (y + z) + y * z;
+}
+
+__global__ void k_fit(const float4* __restrict__ bmin, const float4* __restrict__ bmax, const unsigned* __restrict__ order, int n,
+                      const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
+                      const int2* __restrict__ range, float4* nb_min, float4* nb_max, int* visit,
+                      unsigned char* __restrict__ flags, int max_leaf, float c_node, float c_tri)
+{
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    unsigned p = order[j];
+    float4 a = bmin[p], b = bmax[p];
+    float ha = half_area(a, b);
+    a.w = ha; b.w = ha * c_tri;
+    int id = n - 1 + j;
+    nb_min[id] = a; nb_max[id] = b;
+    flags[id] = 1;
+    int cur = parent[id];
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(&visit[cur], 1) == 0) return;     // first arrival: the sibling finishes the node
+        int lc = left[cur], rc = right[cur];
+        float4 la = __ldcg(nb_min + lc), lb = __ldcg(nb_max + lc), ra = __ldcg(nb_min + rc), rb = __ldcg(nb_max + rc);
+        float4 mn = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.f);
+        float4 mx = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.f);
+        float h = half_area(mn, mx);
+        int2 rg = range[cur];
+        int cnt = rg.y - rg.x + 1;
+        float c_split = c_node * h + lb.w + rb.w;
+        float c_leaf = cnt <= max_leaf ? c_tri * h * (float)cnt : FLT_MAX;
+        bool leaf = c_leaf <= c_split;
+        mn.w = h; mx.w = leaf ? c_leaf : c_split;
+        nb_min[cur] = mn; nb_max[cur] = mx;
+        flags[cur] = leaf ? 1 : 0;
+        cur = parent[cur];
+    }
+}
+
+// ------------------------------------------------------------------ 5. top-down collapse to BVH4
+// One work item = (binary node to open, wide node index to fill).  Greedy surface-area opening: keep
+// replacing the open slot with the largest half-area by its two children until 4 slots are used.
+__device__ __forceinline__ void slot_range(int id, int n, const int2* __restrict__ range, int& first, int& count)
+{
+    if (id >= n - 1) { first = id - (n - 1); count = 1; }
+    else { int2 r = range[id]; first = r.x; count = r.y - r.x + 1; }
+}
+
+__global__ void __launch_bounds__(128) k_collapse(int level, const int2* __restrict__ q_in, int2* __restrict__ q_out, int n,
+                                                  const int* __restrict__ left, const int* __restrict__ right,
+                                                  const int2* __restrict__ range, const float4* __restrict__ nb_min,
+                                                  const float4* __restrict__ nb_max, const unsigned char* __restrict__ flags,
+                                                  float4* __restrict__ nodes, BuildCounters* c)
+{
+    const int items = c->qcount[level];
+    int my_leaves = 0, my_maxleaf = 0;
+    for (int it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
+        int2 item = q_in[it];
+        int slot[4]; int ns;
+        if (flags[item.x]) { slot[0] = item.x; ns = 1; }                 // whole tree is one leaf (tiny meshes)
+        else { slot[0] = left[item.x]; slot[1] = right[item.x]; ns = 2; }
+        while (ns < 4) {
+            int best = -1; float barea = -1.f;
+            for (int k = 0; k < ns; k++) {
+                int id = slot[k];
+                if (id < n - 1 && !flags[id]) { float a = nb_min[id].w; if (a > barea) { barea = a; best = k; } }
+            }
+            if (best < 0) break;
+            int id = slot[best];
+            slot[best] = left[id];
+            slot[ns++] = right[id];
+        }
+        float lo[3][4], hi[3][4]; int ref[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < ns) {
+                int id = slot[k];
+                float4 a = nb_min[id], b = nb_max[id];
+                lo[0][k] = a.x; lo[1][k] = a.y; lo[2][k] = a.z; hi[0][k] = b.x; hi[1][k] = b.y; hi[2][k] = b.z;
+                if (id >= n - 1 || flags[id]) {
+                    int first, count; slot_range(id, n, range, first, count);
+                    ref[k] = ~((first << 3) | (count - 1));
+                    my_leaves++; my_maxleaf = max(my_maxleaf, count);
+                } else {
+                    int w = atomicAdd(&c->n_wide, 1);
+                    int qi = atomicAdd(&c->qcount[level + 1], 1);
+                    q_out[qi] = make_int2(id, w);
+                    ref[k] = w;
+                }
+            } else {
+                // empty slot: lo = hi = +inf can never pass a slab test (an inverted box would: min/max un-invert it)
+                lo[0][k] = lo[1][k] = lo[2][k] = __int_as_float(0x7f800000);
+                hi[0][k] = hi[1][k] = hi[2][k] = __int_as_float(0x7f800000);
+                ref[k] = EMPTY_REF;
+            }
+        }
+        float4* nd = nodes + (size_t)item.y * NODE_F4;
+        nd[0] = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd[1] = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+        nd[2] = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]); nd[3] = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
+        nd[4] = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd[5] = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+        nd[6] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), __int_as_float(ref[2]), __int_as_float(ref[3]));
+        nd[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (my_leaves) { atomicAdd(&c->n_leaves, my_leaves); atomicMax(&c->max_leaf, my_maxleaf); atomicMax(&c->max_level, level); }
+}
+
+// n == 0 / n == 1 trees: a root with no child / one single-primitive leaf
+__global__ void k_trivial_root(float4* nodes, const float4* bmin, const float4* bmax, int n)
+{
+    const float pinf = __int_as_float(0x7f800000);
+    float4 lo = make_float4(pinf, pinf, pinf, pinf), hi = lo;
+    float4 lx = lo, ly = lo, lz = lo, hx = hi, hy = hi, hz = hi;
+    int ref0 = EMPTY_REF;
+    if (n == 1) { lx.x = bmin[0].x; ly.x = bmin[0].y; lz.x = bmin[0].z; hx.x = bmax[0].x; hy.x = bmax[0].y; hz.x = bmax[0].z; ref0 = ~0; }
+    nodes[0] = lx; nodes[1] = hx; nodes[2] = ly; nodes[3] = hy; nodes[4] = lz; nodes[5] = hz;
+    nodes[6] = make_float4(__int_as_float(ref0), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF)); nodes[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+__global__ void k_iota(unsigned* v, int n) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) v[i] = i; }
+__global__ void k_root_sah(const float4* nb_max, BuildCounters* c) { c->sah = nb_max[0].w; }
+
+// ------------------------------------------------------------------ 6. triangle records
+// 64-byte records in leaf order; every derived value uses the unfused ops of point_inside
+// (TrianglePrimitive.hpp:154-162) so the tracer's predicate is bit-identical to the reference's.
+__global__ void k_emit_tris(const rtb_triangle* __restrict__ tris, int n, const unsigned* __restrict__ order,
+                            float4* __restrict__ rec, float2* __restrict__ uvs)
+{
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    unsigned p = order[j];
+    const float* t = (const float*)(tris + p);
+    f3 A = mk3(t[0], t[1], t[2]), B = mk3(t[3], t[4], t[5]), C = mk3(t[6], t[7], t[8]);
+    f3 nrm = mk3(t[9], t[10], t[11]);
+    f3 e0 = xsub(C, A), e1 = xsub(B, A);
+    float4* r = rec + (size_t)j * TRI_F4;
+    r[0] = make_float4(nrm.x, nrm.y, nrm.z, __int_as_float((int)p));
+    r[1] = make_float4(A.x, A.y, A.z, xdot(e0, e0));
+    r[2] = make_float4(e0.x, e0.y, e0.z, xdot(e0, e1));
+    r[3] = make_float4(e1.x, e1.y, e1.z, xdot(e1, e1));
+    float2* u = uvs + (size_t)p * 3;
+    u[0] = make_float2(t[12], t[13]); u[1] = make_float2(t[14], t[15]); u[2] = make_float2(t[16], t[17]);
+}
+
+// ------------------------------------------------------------------ host side
+#define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
+
+cudaError_t mesh_prim_boxes(const rtb_triangle* tris_dev, int n, float4* bmin, float4* bmax, cudaStream_t st)
+{
+    if (n > 0) k_tri_boxes<<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, bmin, bmax);
+    return cudaGetLastError();
+}
+
+cudaError_t mesh_emit(const rtb_triangle* tris_dev, int n, const unsigned* order, float4* tri_rec, float2* uvs, cudaStream_t st)
+{
+    if (n > 0) k_emit_tris<<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, order, tri_rec, uvs);
+    return cudaGetLastError();
+}
+
+template <typename K>
+static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
+                              Arena& ws, BuildCounters* ctr, cudaStream_t st)
+{
+    K* keys[2]; unsigned* vals[2];
+    keys[0] = ws.take<K>(n); keys[1] = ws.take<K>(n);
+    vals[0] = ws.take<unsigned>(n); vals[1] = ws.take<unsigned>(n);
+    const int nblocks = (n + RS_TILE - 1) / RS_TILE;
+    unsigned* hist = ws.take<unsigned>((size_t)256 * nblocks);
+    int* left = ws.take<int>(n); int* right = ws.take<int>(n);
+    int* parent = ws.take<int>(2 * (size_t)n); int2* range = ws.take<int2>(n);
+    int* visit = ws.take<int>(n);
+    float4* nb_min = ws.take<float4>(2 * (size_t)n); float4* nb_max = ws.take<float4>(2 * (size_t)n);
+    unsigned char* flags = ws.take<unsigned char>(2 * (size_t)n);
+    int2* q0 = ws.take<int2>(n); int2* q1 = ws.take<int2>(n);
+    if (!q1) return cudaErrorMemoryAllocation;
+
+    const int g = (n + 255) / 256;
+    k_morton<K><<<g, 256, 0, st>>>(bmin, bmax, n, ctr, keys[0], vals[0]);
+    int cur = radix_sort_pairs<K>(keys, vals, n, key_bits, hist, st);
+    CK(cudaMemcpyAsync(out.order, vals[cur], sizeof(unsigned) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+    k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
+    CK(cudaMemsetAsync(visit, 0, sizeof(int) * (size_t)n, st));
+    k_fit<<<g, 256, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, 1.0f, 1.0f);
+    k_root_sah<<<1, 1, 0, st>>>(nb_max, ctr);
+    // level 0 work item: open binary root into wide node 0
+    int2 root_item = make_int2(0, 0);
+    CK(cudaMemcpyAsync(q0, &root_item, sizeof(int2), cudaMemcpyHostToDevice, st));
+    int one = 1;
+    CK(cudaMemcpyAsync(&ctr->qcount[0], &one, sizeof(int), cudaMemcpyHostToDevice, st));
+    long long width = 1;
+    for (int level = 0; level < 70; level++) {
+        long long items = width < (long long)n ? width : (long long)n;
+        int grid = (int)((items + 127) / 128);
+        if (grid > 148 * 16) grid = 148 * 16;
+        k_collapse<<<grid, 128, 0, st>>>(level, (level & 1) ? q1 : q0, (level & 1) ? q0 : q1, n, left, right, range, nb_min, nb_max,
+                                         flags, out.nodes, ctr);
+        if (width < (long long)n) width *= 4;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t build_bvh(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out, Arena& ws,
+                      cudaStream_t st)
+{
+    // outputs (grow-only)
+    int need_nodes = n > 1 ? n : 1;
+    if (out.node_cap < need_nodes) {
+        if (out.nodes) cudaFree(out.nodes);
+        out.nodes = nullptr; out.node_cap = 0;
+        CK(cudaMalloc((void**)&out.nodes, sizeof(float4) * NODE_F4 * (size_t)need_nodes));
+        out.node_cap = need_nodes;
+    }
+    if (out.order_cap < (n > 0 ? n : 1)) {
+        if (out.order) cudaFree(out.order);
+        out.order = nullptr; out.order_cap = 0;
+        CK(cudaMalloc((void**)&out.order, sizeof(unsigned) * (size_t)(n > 0 ? n : 1)));
+        out.order_cap = n > 0 ? n : 1;
+    }
+    out.n = n;
+    if (max_leaf < 1) max_leaf = 1;
+    if (max_leaf > MAX_LEAF) max_leaf = MAX_LEAF;
+    const bool wide_keys = key_bits > 32;
+    size_t bytes = 4096 + (size_t)(n + 64) * (size_t)((wide_keys ? 16 : 8) + 8 + 4 * 6 + 8 + 64 + 2 + 16) + (size_t)256 * 4 * ((n + RS_TILE - 1) / RS_TILE + 1) + 64 * 256;
+    CK(ws.reserve(bytes));
+    ws.reset();
+    BuildCounters* ctr = ws.take<BuildCounters>(1);
+    k_init_counters<<<1, 96, 0, st>>>(ctr);
+    if (n > 0) k_scene_bounds<<<std::min((n + 255) / 256, 148 * 8), 256, 0, st>>>(bmin, bmax, n, ctr);
+    if (n <= 1) {
+        k_trivial_root<<<1, 1, 0, st>>>(out.nodes, bmin, bmax, n);
+        if (n == 1) k_iota<<<1, 32, 0, st>>>(out.order, 1);
+    } else if (wide_keys) {
+        CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 64, out, ws, ctr, st));
+    } else {
+        CK(build_tree<unsigned>(bmin, bmax, n, max_leaf, 32, out, ws, ctr, st));
+    }
+    BuildCounters h;
+    CK(cudaMemcpyAsync(&h, ctr, sizeof h, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    auto dec = [](int i) { int j = i >= 0 ? i : i ^ 0x7fffffff; float f; memcpy(&f, &j, 4); return f; };
+    for (int k = 0; k < 6; k++) out.bounds[k] = dec(h.bounds[k]);
+    if (n <= 1) { out.num_nodes = 1; out.num_leaves = n; out.max_leaf = n; out.depth = 1; out.sah = 0.f; }
+    else {
+        out.num_nodes = h.n_wide; out.num_leaves = h.n_leaves; out.max_leaf = h.max_leaf; out.depth = h.max_level + 1; out.sah = h.sah;
+        if (h.qcount[70] != 0) return cudaErrorLaunchFailure;      // tree deeper than the level loop: refuse, never truncate
+    }
+    return cudaSuccess;
+}
+
+}  // namespace rtb

@@ -1,0 +1,41 @@
+// rtb_build.cuh -- host interface of the on-device LBVH builder (rtb_build.cu).
+#pragma once
+#include "rtb_internal.cuh"
+#include <vector>
+
+namespace rtb {
+
+// Grow-only device arena so per-frame rebuilds (C5) do not call cudaMalloc.
+struct Arena {
+    char* base = nullptr;
+    size_t cap = 0, used = 0;
+    cudaError_t reserve(size_t bytes);
+    template <typename T> T* take(size_t count)
+    {
+        size_t off = (used + 255) & ~(size_t)255;
+        used = off + count * sizeof(T);
+        return used <= cap ? (T*)(base + off) : nullptr;
+    }
+    void reset() { used = 0; }
+    void release();
+};
+
+struct BvhResult {
+    float4* nodes = nullptr;        // device, capacity node_cap wide nodes
+    unsigned* order = nullptr;      // device, sorted slot -> primitive index
+    int node_cap = 0, order_cap = 0;
+    int n = 0, num_nodes = 0, num_leaves = 0, max_leaf = 0, depth = 0;
+    float bounds[6] = { 0, 0, 0, 0, 0, 0 };
+    float sah = 0.f;
+};
+
+// Builds a wide BVH over n primitive boxes (device float4 arrays, w ignored).  Asynchronous on `st`
+// except for one small read-back of the build counters at the end.
+cudaError_t build_bvh(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
+                      Arena& ws, cudaStream_t st);
+
+// Triangle-mesh front/back ends.
+cudaError_t mesh_prim_boxes(const rtb_triangle* tris_dev, int n, float4* bmin, float4* bmax, cudaStream_t st);
+cudaError_t mesh_emit(const rtb_triangle* tris_dev, int n, const unsigned* order, float4* tri_rec, float2* uvs, cudaStream_t st);
+
+}  // namespace rtb

@@ -1,0 +1,122 @@
+// rtb_sort.cuh -- device LSD radix sort of (Morton key, primitive index) pairs, 8 bits per pass.
+//
+// Hand-written (no CUB/Thrust).  Per pass: (1) per-tile digit histogram, (2) exclusive scan of the
+// digit-major histogram table, (3) stable scatter.  The scatter ranks keys inside a tile with
+// warp-synchronous __match_any_sync multi-split: each warp owns 32*KPT consecutive keys, ranks them
+// round by round against per-warp digit counters in shared memory, then the 256 digit columns are
+// prefix-summed across the tile's warps.  HBM-bound streaming work: 2 key reads + 1 pair read/write per pass.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtb {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_KPT = 16;
+constexpr int RS_TILE = RS_THREADS * RS_KPT;   // 4096 keys per block
+
+template <typename K>
+__global__ void __launch_bounds__(RS_THREADS) rs_hist(const K* __restrict__ keys, int n, int shift, int nblocks,
+                                                       unsigned* __restrict__ hist)
+{
+    __shared__ unsigned h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * RS_TILE;
+#pragma unroll 4
+    for (int r = 0; r < RS_KPT; r++) {
+        int i = base + r * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(unsigned)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of `total` unsigned values in place, one block of 1024 threads
+__global__ void __launch_bounds__(1024) rs_scan(unsigned* __restrict__ data, int total)
+{
+    __shared__ unsigned part[1024];
+    const int t = threadIdx.x;
+    const int per = (total + 1023) / 1024;
+    const int b = t * per, e = min(b + per, total);
+    unsigned s = 0;
+    for (int i = b; i < e; i++) s += data[i];
+    part[t] = s;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {         // Hillis-Steele inclusive scan
+        unsigned v = t >= off ? part[t - off] : 0u;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    unsigned run = part[t] - s;
+    for (int i = b; i < e; i++) { unsigned v = data[i]; data[i] = run; run += v; }
+}
+
+template <typename K>
+__global__ void __launch_bounds__(RS_THREADS) rs_scatter(const K* __restrict__ keys_in, const unsigned* __restrict__ vals_in,
+                                                         K* __restrict__ keys_out, unsigned* __restrict__ vals_out, int n,
+                                                         int shift, int nblocks, const unsigned* __restrict__ offs)
+{
+    __shared__ unsigned cnt[RS_WARPS][256];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    const int wbase = blockIdx.x * RS_TILE + w * (32 * RS_KPT);
+    K key[RS_KPT];
+    unsigned short off[RS_KPT];
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < RS_KPT; r++) {
+        int i = wbase + r * 32 + lane;
+        key[r] = i < n ? keys_in[i] : (K)0;
+    }
+#pragma unroll
+    for (int r = 0; r < RS_KPT; r++) {
+        int i = wbase + r * 32 + lane;
+        unsigned d = i < n ? ((unsigned)(key[r] >> shift) & 255u) : 256u;
+        unsigned peers = __match_any_sync(0xffffffffu, d);
+        int leader = __ffs(peers) - 1;
+        unsigned old = 0;
+        if (lane == leader && d < 256u) { old = cnt[w][d]; cnt[w][d] = old + __popc(peers); }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        off[r] = (unsigned short)(old + __popc(peers & lt));
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // digit column prefix across warps, seeded with this tile's global offset
+        const int d = threadIdx.x;
+        unsigned run = offs[(size_t)d * nblocks + blockIdx.x];
+#pragma unroll
+        for (int ww = 0; ww < RS_WARPS; ww++) { unsigned c = cnt[ww][d]; cnt[ww][d] = run; run += c; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RS_KPT; r++) {
+        int i = wbase + r * 32 + lane;
+        if (i < n) {
+            unsigned d = (unsigned)(key[r] >> shift) & 255u;
+            unsigned pos = cnt[w][d] + off[r];
+            keys_out[pos] = key[r];
+            vals_out[pos] = vals_in[i];
+        }
+    }
+}
+
+// Sorts `bits` low bits; result ends in (keys[0], vals[0]) or (keys[1], vals[1]); returns which.
+template <typename K>
+inline int radix_sort_pairs(K* keys[2], unsigned* vals[2], int n, int bits, unsigned* hist, cudaStream_t st)
+{
+    const int nblocks = (n + RS_TILE - 1) / RS_TILE;
+    int cur = 0;
+    for (int shift = 0; shift < bits; shift += 8) {
+        rs_hist<K><<<nblocks, RS_THREADS, 0, st>>>(keys[cur], n, shift, nblocks, hist);
+        rs_scan<<<1, 1024, 0, st>>>(hist, 256 * nblocks);
+        rs_scatter<K><<<nblocks, RS_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, nblocks, hist);
+        cur ^= 1;
+    }
+    return cur;
+}
+
+}  // namespace rtb
