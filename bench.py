@@ -1,0 +1,382 @@
+#!/usr/bin/env python
+"""bench.py -- Mrays/s of the B200 ray-casting core on the BASELINE.json configs (default: C3, the 4K
+instanced scene the metric is quoted on: 100 MeshInstances of a 1M-triangle BLAS, reflections to depth 4).
+
+    python bench.py --gpus N --steps K --warmup W [--config c1|c2|c3|c4|c5] [--impl reference]
+
+One process per GPU (torchrun for N>1).  A step = one frame of the hot path (camera rays -> TLAS/BLAS
+traversal -> shading -> framebuffer; multi-GPU: + NCCL gather of the image bands to rank 0).  The camera
+orbits so every step is a different frame; L2 is flushed (untimed) between steps.  Prints ONE JSON line.
+torch is used for device buffers, streams, events and torch.distributed only.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from cuda_raytracing_b200 import synth  # noqa: E402
+
+CONFIGS = {
+    # name: (width, height, mesh (N, M), ground, instances, mode, max_depth, spp, K scale, description)
+    "c1": dict(w=640, h=480, mesh=(132, 264), ground=False, grid=None, mode=0, depth=0, spp=1, K="c1",
+               desc="C1 69,696-tri OBJ mesh, 640x480, primary closest hit"),
+    "c2": dict(w=1920, h=1080, mesh=(500, 1000), ground=True, grid=None, mode=1, depth=0, spp=1, K="ref",
+               desc="C2 1M-tri mesh + ground, 1080p, primary + shadow rays"),
+    "c3": dict(w=3840, h=2160, mesh=(500, 1000), ground=False, grid=(10, 10), mode=2, depth=4, spp=1, K="ref2",
+               desc="C3 4K, 100 instances of a 1M-tri BLAS, mirror reflections to depth 4"),
+    "c4": dict(w=7680, h=4320, mesh=(500, 1000), ground=False, grid=(10, 10), mode=3, depth=8, spp=64, K="ref4",
+               desc="C4 8K diffuse path tracing, 64 spp, 8 bounces, 100 instances of a 1M-tri BLAS"),
+    "c5": dict(w=3840, h=2160, mesh=(1582, 3161), ground=False, grid=None, mode=1, depth=0, spp=1, K="ref2",
+               desc="C5 per-frame LBVH rebuild of an animated 10M-tri mesh + 4K primary+shadow render"),
+}
+
+
+def config_K(cfg):
+    if cfg["K"] == "c1":
+        return synth.C1_K.copy(), synth.ZERO_D.copy()
+    s = {"ref": 1.0, "ref2": 2.0, "ref4": 4.0}[cfg["K"]]
+    K = synth.REF_K.copy()
+    K[:2, :] *= np.float32(s)
+    return K, synth.REF_D.copy()
+
+
+def camera_pose(cfg, step):
+    """Orbiting camera that keeps the geometry in frame (benchmark cameras must frame the mesh)."""
+    a = 0.05 * step
+    if cfg["grid"] is None:
+        r = 2.6
+        x, y, z = r * math.sin(a), -r * math.cos(a), 1.6
+        return (x, y, z, -a, -0.22, 0.0)
+    r = 19.0
+    x, y, z = r * math.sin(a), -r * math.cos(a), 9.0
+    return (x, y, z, -a, -0.42, 0.0)
+
+
+def scene_materials(cfg):
+    if cfg["mode"] == 2:
+        return [dict(albedo=(0.9, 0.6, 0.3), metallic=0.6), dict(albedo=(0.3, 0.8, 0.4), metallic=0.35)]
+    return [dict(albedo=(0.1, 0.2, 0.9), metallic=0.0), dict(albedo=(0.7, 0.7, 0.7), metallic=0.0)]
+
+
+def scene_instances(cfg):
+    if cfg["grid"] is None:
+        return [(0, 0, (0.0, 0.0, 0.0, 0.0, 0.0, 0.0), (1.0, 1.0, 1.0))]
+    poses = synth.instance_grid(*cfg["grid"])
+    return [(0, i % 2, p, (1.0, 1.0, 1.0)) for i, p in enumerate(poses)]
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+def build_tris(cfg, phase=0.0):
+    return synth.bumpy_sphere(cfg["mesh"][0], cfg["mesh"][1], phase=phase, ground=cfg["ground"])
+
+
+# ------------------------------------------------------------------------------------------- reference arm
+def run_reference(args, cfg, rank):
+    """The reference's own CPU implementation of the path on the host cores (oracle/_ref when present, else the
+    oracle port), bounded sample per step: a centred band of rows of the same frame."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import orc
+    K, D = config_K(cfg)
+    cores = os.cpu_count() or 1
+    tris = build_tris(cfg)
+    mats, insts = scene_materials(cfg), scene_instances(cfg)
+    use_ref = orc.RefHost.available() and cfg["mode"] == 0 and len(tris) <= 200000
+    O = orc.Oracle()
+    if use_ref:
+        R = orc.RefHost()
+        mh = R.mesh_create(tris)
+        sc = R.scene([mh], mats, insts)
+        kind = "reference"
+    else:
+        om = O.mesh_create(tris)
+        sc = orc.OracleScene(O, [om], mats, [O.build_instance(m, a, p, s) for (m, a, p, s) in insts])
+        kind = "port"
+    W, H = cfg["w"], cfg["h"]
+    spp = min(cfg["spp"], 2)
+
+    def one(step, rows):
+        y0 = max(0, H // 2 - rows // 2)
+        pose = camera_pose(cfg, step)
+        t0 = time.perf_counter()
+        if use_ref:
+            R.render(sc, W, H, K, D, pose, nthreads=cores, y0=y0, y1=y0 + rows)
+            rays = rows * W
+        else:
+            out = sc.render(W, H, K, D, pose, mode=cfg["mode"], max_depth=cfg["depth"], spp=spp, y0=y0, y1=y0 + rows,
+                            nthreads=cores, aovs=False, stats=True)
+            rays = out["stats"]["rays"]
+        return rays, time.perf_counter() - t0
+
+    rows = 8
+    rays, dt = one(0, rows)                                  # calibrate: aim at ~3 s of CPU work per step
+    rows = int(max(8, min(H, rows * 3.0 / max(dt, 1e-3))))
+    for s in range(args.warmup):
+        one(s, rows)
+    tot_r, tot_t = 0, 0.0
+    for s in range(args.steps):
+        r, dt = one(args.warmup + s, rows)
+        tot_r += r
+        tot_t += dt
+    val = tot_r / tot_t / 1e6
+    sample = "%d centred rows of %dx%d per step (%s), %d spp" % (rows, W, H, cfg["desc"], spp)
+    line = dict(impl="reference", metric="Mrays/s", value=val, unit="Mrays/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                ms_per_step=1e3 * tot_t / max(1, args.steps), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+                data="synthetic", config=dict(workload=cfg["desc"], config=args.config),
+                cpu_baseline=dict(value=val, unit="Mrays/s", cores=cores, kind=kind, sample=sample),
+                e2e=dict(value=val, unit="Mrays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------- our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--config", default="c3")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--no-flush", action="store_true")
+    args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, cfg, rank)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from cuda_raytracing_b200 import api
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    W, H = cfg["w"], cfg["h"]
+    K, D = config_K(cfg)
+
+    # ---- scene (replicated on every rank) -------------------------------------------------------
+    tris = build_tris(cfg)
+    scene = api.Scene(local_rank)
+    for m in scene_materials(cfg):
+        scene.add_material(api.Material(albedo=m["albedo"], metallic=m["metallic"]))
+    tris_t = torch.from_numpy(tris.view(np.uint8).reshape(-1, 72)).to(dev)      # triangles resident in HBM
+    mesh = api.MeshPrimitive(tris[:0])
+    mesh.device_ptr, mesh.num_triangles = tris_t.data_ptr(), len(tris)
+    scene.add_mesh(mesh)
+    for (mi, ma, pose, scale) in scene_instances(cfg):
+        scene.add_mesh_instance(api.MeshInstance(mi, ma, pose, scale))
+    scene.upload_to_device()
+    info = scene.mesh_info(0)
+
+    cam = api.Camera(W, H, K, D)
+    cam.mode, cam.max_depth, cam.spp = cfg["mode"], cfg["depth"], cfg["spp"]
+    cam.tile_rank, cam.tile_count = rank, world
+    pitch = W * 3
+    frame = torch.zeros((H, pitch), dtype=torch.uint8, device=dev)
+    from cuda_raytracing_b200 import tiles
+    fg = tiles.FrameGather(H, pitch, rank, world, dev)
+    stream = torch.cuda.current_stream()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    host_frame = torch.empty((H, pitch), dtype=torch.uint8).pin_memory()
+
+    def step(i, e2e=False):
+        """one frame: (C5: rebuild) -> render own bands -> gather to rank 0 (-> D2H when e2e)."""
+        if args.config == "c5":
+            # animated mesh: new vertex positions arrive in HBM, BLAS is rebuilt on the device
+            scene.rebuild_mesh(0, device_ptr=anim[i % len(anim)].data_ptr(), n=len(tris))
+        cam.pose = np.array(camera_pose(cfg, i), np.float32)
+        cam.render_scene(scene, frame.data_ptr(), pitch, stream=C.c_void_p(stream.cuda_stream))
+        fg.gather(frame)
+        if e2e and rank == 0:
+            host_frame.copy_(frame, non_blocking=True)
+            stream.synchronize()
+
+    anim = None
+    if args.config == "c5":
+        anim = []
+        for f in range(2):
+            t = build_tris(cfg, phase=2 * math.pi * f / 60.0)
+            anim.append(torch.from_numpy(t.view(np.uint8).reshape(-1, 72)).to(dev))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(e2e):
+        for i in range(args.warmup):
+            step(i, e2e)
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        rays = 0
+        launches = 0
+        t_wall0 = time.perf_counter()
+        for k in range(args.steps):
+            if not args.no_flush:
+                flush.fill_(k & 0xFF)                       # L2 flush, outside the timed events
+            barrier()
+            ev[k][0].record(stream)
+            step(args.warmup + k, e2e)
+            ev[k][1].record(stream)
+            barrier()
+            st = scene.frame_stats()
+            rays += st["rays"]
+            launches += st["launches"]
+        t_wall = time.perf_counter() - t_wall0
+        clocks = sampler.stop()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        t = torch.tensor([ms, float(rays)], dtype=torch.float64, device=dev)
+        if world > 1:
+            tmax = t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            tsum = t.clone()
+            dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+            ms, rays = float(tmax[0]), float(tsum[1])
+        return ms, rays, launches, clocks, t_wall
+
+    ms, rays, launches, clocks, _ = timed(False)
+    ms_e, rays_e, _, _, _ = timed(True)
+    value = rays / (ms * 1e-3) / 1e6
+    e2e_value = rays_e / (ms_e * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel (trace+shade): algorithmic bytes from the traversal counters ----
+    peak, peak_kind = load_peaks()
+    roof = None
+    cpu = None
+    ref_cuda = None
+    if rank == 0:
+        scene.set_option("counters", 1)
+        cam.tile_rank, cam.tile_count = 0, 1
+        cam.pose = np.array(camera_pose(cfg, args.warmup), np.float32)
+        cam.render_scene(scene, frame.data_ptr(), pitch, synchronize=True)
+        st = scene.frame_stats()
+        scene.set_option("counters", 0)
+        queue_hops = max(0, st["rays"] - W * H * (cfg["spp"] if cfg["mode"] == 3 else 1)) if cfg["mode"] >= 2 else 0
+        alg_bytes = st["nodes"] * 128 + st["tris"] * 64 + W * H * 3 + queue_hops * 64
+        # time the same full frame on the same stream
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        flush.fill_(1)
+        e0.record(stream)
+        cam.render_scene(scene, frame.data_ptr(), pitch, stream=C.c_void_p(stream.cuda_stream))
+        e1.record(stream)
+        torch.cuda.synchronize()
+        kms = e0.elapsed_time(e1)
+        ach = alg_bytes / (kms * 1e-3) / 1e9
+        roof = dict(bound="hbm", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None, peak_kind=peak_kind,
+                    kernel="k_wave/k_render_direct (trace+shade)", kernel_ms=kms, nodes_per_ray=st["nodes"] / max(1, st["rays"]),
+                    tris_per_ray=st["tris"] / max(1, st["rays"]), rays=st["rays"], alg_bytes=alg_bytes,
+                    note="algorithmic bytes = 128 B/node visit + 64 B/triangle test + 3 B/pixel + 64 B/queue hop; the BLAS "
+                         "(~110 MB) is L2-resident, so achieved can exceed the HBM copy peak")
+        cam.tile_rank, cam.tile_count = rank, world
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import orc
+        O = orc.Oracle()
+        cores = os.cpu_count() or 1
+        om = O.mesh_create(tris)
+        osc = orc.OracleScene(O, [om], scene_materials(cfg), [O.build_instance(m, a, p, s) for (m, a, p, s) in scene_instances(cfg)])
+        rows, y0 = 8, H // 2
+        pose = camera_pose(cfg, args.warmup)
+        spp = min(cfg["spp"], 2)
+        t0 = time.perf_counter()
+        out = osc.render(W, H, K, D, pose, mode=cfg["mode"], max_depth=cfg["depth"], spp=spp, y0=y0, y1=y0 + rows, nthreads=cores, aovs=False, stats=True)
+        dt = time.perf_counter() - t0
+        rows = int(max(8, min(H, rows * 12.0 / max(dt, 1e-3))))
+        y0 = max(0, H // 2 - rows // 2)
+        t0 = time.perf_counter()
+        out = osc.render(W, H, K, D, pose, mode=cfg["mode"], max_depth=cfg["depth"], spp=spp, y0=y0, y1=y0 + rows, nthreads=cores, aovs=False, stats=True)
+        dt = time.perf_counter() - t0
+        cpu = dict(value=out["stats"]["rays"] / dt / 1e6, unit="Mrays/s", cores=cores, kind="port",
+                   sample="%d centred rows of the %dx%d frame (%.1f s), oracle/rt_oracle.c on %d threads" % (rows, W, H, dt, cores))
+        if not args.no_ref_cuda and orc.RefHost.available() and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref_cuda.so")):
+            try:
+                sys.path.insert(0, os.path.join(ROOT, "tests"))
+                import refcuda
+                ref_cuda = refcuda.time_reference_kernel(tris, scene_materials(cfg), scene_instances(cfg), W, H, K, D, pose)
+            except Exception as ex:                      # the reported baseline is optional, the bench line is not
+                ref_cuda = dict(error=str(ex)[:200])
+
+    if rank == 0:
+        line = dict(metric="Mrays/s", value=value, unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
+                    config=dict(workload=cfg["desc"], config=args.config, width=W, height=H, triangles=int(len(tris)),
+                                instances=len(scene_instances(cfg)), mode=cfg["mode"], max_depth=cfg["depth"], spp=cfg["spp"],
+                                parallelism="image bands of %d rows interleaved over %d GPU(s), scene replicated, NCCL gather to rank 0" % (api.BAND_ROWS, world),
+                                l2="flushed between steps with a 256 MiB write (untimed)" if not args.no_flush else "not flushed",
+                                rays_per_frame=rays / args.steps, blas=dict(nodes=info["num_nodes"], leaves=info["num_leaves"], depth=info["depth"],
+                                                                         build_ms=info["build_ms"], bytes=info["device_bytes"])),
+                    clocks=clocks, gpu_launches=launches,
+                    e2e=dict(value=e2e_value, unit="Mrays/s", h2d_bytes_per_step=int(C.sizeof(api.RenderParams)), d2h_bytes_per_step=int(H * pitch),
+                             ms_per_step=ms_e / args.steps),
+                    roofline=roof, cpu_baseline=cpu)
+        if ref_cuda is not None:
+            line["ref_cuda"] = ref_cuda
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    scene.close()
+
+
+if __name__ == "__main__":
+    main()

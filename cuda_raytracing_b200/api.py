@@ -53,13 +53,13 @@ class MeshInfo(C.Structure):
 
 class FrameStats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
-                ("device_ms", C.c_float), ("overflow", C.c_int)]
+                ("device_ms", C.c_float), ("overflow", C.c_int), ("launches", C.c_int)]
 
 
 assert C.sizeof(CInstance) == 104 and C.sizeof(CMaterial) == 48 and C.sizeof(Lre) == 24
 
 EXPORTS = ["rtb_context_create", "rtb_context_destroy", "rtb_last_error", "rtb_version", "rtb_set_option",
-           "rtb_mesh_create", "rtb_mesh_rebuild", "rtb_mesh_info_get", "rtb_mesh_destroy", "rtb_texture_upload",
+           "rtb_mesh_create", "rtb_mesh_rebuild", "rtb_mesh_info_get", "rtb_mesh_read", "rtb_mesh_destroy", "rtb_texture_upload",
            "rtb_set_materials", "rtb_set_instances", "rtb_update_instance", "rtb_render", "rtb_render_host",
            "rtb_synchronize", "rtb_frame_stats_get", "rtb_invert_intrinsic", "rtb_invert_lre",
            "rtb_instance_build_inv", "rtb_triangle_init", "rtb_obj_load", "rtb_free"]
@@ -90,6 +90,7 @@ def lib():
     L.rtb_mesh_rebuild.argtypes = [vp, ci, vp, ci, ci]
     L.rtb_mesh_info_get.argtypes = [vp, ci, C.POINTER(MeshInfo)]
     L.rtb_mesh_destroy.argtypes = [vp, ci]
+    L.rtb_mesh_read.argtypes = [vp, ci, ci, vp, C.c_size_t]
     L.rtb_texture_upload.argtypes = [vp, vp, ci, ci, C.POINTER(vp), C.POINTER(C.c_size_t)]
     L.rtb_set_materials.argtypes = [vp, vp, ci]
     L.rtb_set_instances.argtypes = [vp, vp, ci]
@@ -271,10 +272,20 @@ class Scene:
         _check(lib().rtb_mesh_info_get(self._ctx, self.mesh_ids[index], C.byref(info)))
         return {f: (list(getattr(info, f)) if f.startswith("bounds") else getattr(info, f)) for f, _ in MeshInfo._fields_}
 
+    def mesh_arrays(self, index):
+        """Download the wide nodes (N,8,4 float32), triangle records (T,4,4 float32) and leaf order (T uint32)."""
+        info = self.mesh_info(index)
+        nodes = np.zeros((info["num_nodes"], 8, 4), np.float32)
+        tris = np.zeros((info["num_triangles"], 4, 4), np.float32)
+        order = np.zeros(info["num_triangles"], np.uint32)
+        for what, arr in ((0, nodes), (1, tris), (2, order)):
+            _check(lib().rtb_mesh_read(self._ctx, self.mesh_ids[index], what, arr.ctypes.data, arr.nbytes))
+        return nodes, tris, order
+
     def frame_stats(self):
         st = FrameStats()
         _check(lib().rtb_frame_stats_get(self._ctx, C.byref(st)))
-        return dict(rays=st.rays, nodes=st.nodes_visited, tris=st.tris_tested, device_ms=st.device_ms)
+        return dict(rays=st.rays, nodes=st.nodes_visited, tris=st.tris_tested, device_ms=st.device_ms, launches=st.launches)
 
     def synchronize(self):
         _check(lib().rtb_synchronize(self._ctx))

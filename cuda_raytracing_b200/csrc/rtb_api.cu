@@ -21,6 +21,8 @@ static int cuda_fail(cudaError_t e, const char* where)
 }
 #define CU(x, where) do { cudaError_t _e = (x); if (_e != cudaSuccess) return cuda_fail(_e, where); } while (0)
 
+namespace rtb { void wave_release(void* state); }
+
 struct MeshRec {
     bool alive = false;
     int n = 0;
@@ -50,6 +52,7 @@ struct rtb_context {
     int32_t* aov_prim_d = nullptr; int32_t* aov_inst_d = nullptr; float* aov_t_d = nullptr; size_t aov_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
+    int last_launches = 0;
     int opt_counters = 0, opt_leaf = 4, opt_key_bits = 0;
     void* wf = nullptr;            // wavefront state (rtb_wavefront.cu)
 };
@@ -91,7 +94,6 @@ static void free_mesh(MeshRec& m)
     m = MeshRec();
 }
 
-void rtb_wavefront_release(rtb_context* c);
 
 void rtb_context_destroy(rtb_context* c)
 {
@@ -112,7 +114,7 @@ void rtb_context_destroy(rtb_context* c)
     if (c->aov_prim_d) cudaFree(c->aov_prim_d);
     if (c->aov_inst_d) cudaFree(c->aov_inst_d);
     if (c->aov_t_d) cudaFree(c->aov_t_d);
-    rtb_wavefront_release(c);
+    wave_release(c->wf);
     c->ws.release(); c->stage.release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -199,6 +201,21 @@ int rtb_mesh_info_get(rtb_context* c, int id, rtb_mesh_info* out)
     return RTB_OK;
 }
 
+int rtb_mesh_read(rtb_context* c, int id, int what, void* out, size_t bytes)
+{
+    if (!c || !out || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive) return fail(RTB_ERR_INVALID, "rtb_mesh_read: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    const MeshRec& m = c->meshes[id];
+    const void* src = nullptr; size_t have = 0;
+    if (what == 0) { src = m.bvh.nodes; have = sizeof(float4) * NODE_F4 * (size_t)m.bvh.num_nodes; }
+    else if (what == 1) { src = m.tri_rec; have = sizeof(float4) * TRI_F4 * (size_t)m.n; }
+    else if (what == 2) { src = m.bvh.order; have = sizeof(unsigned) * (size_t)m.n; }
+    else return fail(RTB_ERR_INVALID, "rtb_mesh_read: unknown array");
+    if (bytes < have) return fail(RTB_ERR_INVALID, "rtb_mesh_read: output buffer too small");
+    if (have) CU(cudaMemcpy(out, src, have, cudaMemcpyDeviceToHost), "rtb_mesh_read copy");
+    return RTB_OK;
+}
+
 int rtb_mesh_destroy(rtb_context* c, int id)
 {
     if (!c || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive) return fail(RTB_ERR_INVALID, "rtb_mesh_destroy: bad argument");
@@ -212,7 +229,7 @@ int rtb_mesh_destroy(rtb_context* c, int id)
 }  // extern "C"
 
 // ------------------------------------------------------------------ scene
-namespace rtb { cudaError_t launch_wavefront(rtb_context* c, void** wf_state, const SceneDev& sc, const FrameParams& P, unsigned char* img,
+namespace rtb { extern int g_wave_launches; cudaError_t launch_wavefront(rtb_context* c, void** wf_state, const SceneDev& sc, const FrameParams& P, unsigned char* img,
                                              size_t pitch, const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st); }
 
 extern "C" {
@@ -391,9 +408,13 @@ static int render_impl(rtb_context* c, const rtb_render_params* p, unsigned char
     if (aovs) a = *aovs;
     CU(cudaMemsetAsync(c->counters_d, 0, sizeof(Counters), st), "counters reset");
     if (p->mode == RTB_MODE_REFERENCE || p->mode == RTB_MODE_SHADOW)
+    {
         CU(launch_render(sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "render launch");
-    else
+        c->last_launches = 1;
+    } else {
         CU(launch_wavefront(c, &c->wf, sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "wavefront launch");
+        c->last_launches = g_wave_launches;
+    }
     return RTB_OK;
 }
 
@@ -466,6 +487,7 @@ int rtb_frame_stats_get(rtb_context* c, rtb_frame_stats* out)
     Counters h;
     CU(cudaMemcpy(&h, c->counters_d, sizeof h, cudaMemcpyDeviceToHost), "counters");
     out->rays = h.rays; out->nodes_visited = h.nodes; out->tris_tested = h.tris; out->device_ms = c->last_ms; out->overflow = h.overflow;
+    out->launches = c->last_launches;
     if (h.overflow) return fail(RTB_ERR_OVERFLOW, "render: traversal stack / ray queue overflow");
     return RTB_OK;
 }

@@ -67,7 +67,7 @@ typedef struct {
     rtb_lre inv_pose;          /* invert_lre(pose) (Camera.cu:21)                                      */
     int mode, max_depth, spp;
     uint32_t seed;
-    int tile_rank, tile_count; /* multi-GPU image partition: this call renders the 64-row bands b with
+    int tile_rank, tile_count; /* multi-GPU image partition: this call renders the 8-row bands b with
                                   b % tile_count == tile_rank (0,1 = whole image)                      */
 } rtb_render_params;
 
@@ -89,6 +89,7 @@ typedef struct {
     uint64_t tris_tested;      /* triangle records fetched                                                  */
     float device_ms;           /* cudaEvent time of the last rtb_render_host / rtb_render_timed             */
     int overflow;              /* traversal stack or queue overflow flag (render fails loudly)              */
+    int launches;              /* kernels of this library launched by the last rtb_render                   */
 } rtb_frame_stats;
 
 /* ---- context ------------------------------------------------------------------------------ */
@@ -105,6 +106,9 @@ RTB_API int rtb_mesh_create(rtb_context* ctx, const rtb_triangle* tris, int n, i
 RTB_API int rtb_mesh_rebuild(rtb_context* ctx, int mesh_id, const rtb_triangle* tris, int n, int tris_on_device);
 RTB_API int rtb_mesh_info_get(rtb_context* ctx, int mesh_id, rtb_mesh_info* out);
 RTB_API int rtb_mesh_destroy(rtb_context* ctx, int mesh_id);
+/* Inspection (tools/tests; the analogue of BVHTree::print_stats, BVHTree.hpp:117-172): copies device arrays to the host.
+ * what = 0: wide nodes (num_nodes * 128 B), 1: triangle records (num_triangles * 64 B), 2: leaf order (num_triangles * 4 B) */
+RTB_API int rtb_mesh_read(rtb_context* ctx, int mesh_id, int what, void* out, size_t bytes);
 
 /* ---- scene: replaces Scene::upload_to_device (Scene.cpp:25-65) / update_mesh_instance (67-74),
  *      Material::to_device (Material.hpp:21-27) and the texel half of upload_texture (29-43). ------ */
