@@ -61,7 +61,7 @@ assert C.sizeof(CInstance) == 104 and C.sizeof(CMaterial) == 48 and C.sizeof(Lre
 EXPORTS = ["rtb_context_create", "rtb_context_destroy", "rtb_last_error", "rtb_version", "rtb_set_option",
            "rtb_mesh_create", "rtb_mesh_rebuild", "rtb_mesh_info_get", "rtb_mesh_read", "rtb_mesh_destroy", "rtb_texture_upload",
            "rtb_set_materials", "rtb_set_instances", "rtb_update_instance", "rtb_render", "rtb_render_host",
-           "rtb_synchronize", "rtb_frame_stats_get", "rtb_invert_intrinsic", "rtb_invert_lre",
+           "rtb_synchronize", "rtb_frame_stats_get", "rtb_debug_math", "rtb_invert_intrinsic", "rtb_invert_lre",
            "rtb_instance_build_inv", "rtb_triangle_init", "rtb_obj_load", "rtb_free"]
 
 _lib = None
@@ -99,6 +99,7 @@ def lib():
     L.rtb_render_host.argtypes = [vp, C.POINTER(RenderParams), vp, C.c_size_t, C.POINTER(Aovs)]
     L.rtb_synchronize.argtypes = [vp]
     L.rtb_frame_stats_get.argtypes = [vp, C.POINTER(FrameStats)]
+    L.rtb_debug_math.argtypes = [vp, ci, vp, vp, ci]
     L.rtb_invert_intrinsic.argtypes = [vp, vp]
     L.rtb_invert_intrinsic.restype = None
     L.rtb_invert_lre.argtypes = [C.POINTER(Lre), C.POINTER(Lre)]
@@ -281,6 +282,12 @@ class Scene:
         for what, arr in ((0, nodes), (1, tris), (2, order)):
             _check(lib().rtb_mesh_read(self._ctx, self.mesh_ids[index], what, arr.ctypes.data, arr.nbytes))
         return nodes, tris, order
+
+    def debug_math(self, what, x):
+        x = np.ascontiguousarray(x, np.float32)
+        out = np.zeros_like(x)
+        _check(lib().rtb_debug_math(self._ctx, what, x.ctypes.data, out.ctypes.data, x.size))
+        return out
 
     def frame_stats(self):
         st = FrameStats()

@@ -65,4 +65,46 @@ XF f3 xapply_quat(float4 q, f3 v)
                xa(xs(xs(xm(q.x, d), xm(q.w, a)), xm(q.y, c)), xm(q.z, b)));
 }
 
+// atanf with the bits of the host libm the reference's host path calls at raycast.cu:170 (`atan(radius)`).
+// glibc 2.39 (this image and the GPU box) implements atanf with the FreeBSD/fdlibm single-precision
+// algorithm (argument reduction to |x| < 7/16 via atan(0.5), atan(1), atan(1.5), atan(inf) + an 11-term
+// odd/even polynomial).  Restated here with unfused float ops; checked bit-identical to glibc's atanf on
+// 5e7 random arguments in [0,4] (tests/test_oracle_cpu.py keeps a sampled fixture of that check).  CUDA's
+// own atanf differs from it by 1 ulp on ~6 % of arguments, which is enough to move a grazing-angle hit
+// distance by more than the 1e-5 tolerance.
+XF float xatanf(float x)
+{
+    const float hi[4] = { 4.6364760399e-01f, 7.8539812565e-01f, 9.8279368877e-01f, 1.5707962513e+00f };
+    const float lo[4] = { 5.0121582440e-09f, 3.7748947079e-08f, 3.4473217170e-08f, 7.5497894159e-08f };
+    const int hx = __float_as_int(x), ix = hx & 0x7fffffff;
+    if (ix >= 0x4c000000) {                         // |x| >= 2^25 or NaN
+        if (ix > 0x7f800000) return xa(x, x);
+        return hx > 0 ? xa(hi[3], lo[3]) : xs(-hi[3], lo[3]);
+    }
+    int id;
+    if (ix < 0x3ee00000) {                          // |x| < 0.4375
+        if (ix < 0x31000000) return x;              // |x| < 2^-29
+        id = -1;
+    } else {
+        x = fabsf(x);
+        if (ix < 0x3f980000) {
+            if (ix < 0x3f300000) { id = 0; x = xd(xs(xm(2.0f, x), 1.0f), xa(2.0f, x)); }
+            else { id = 1; x = xd(xs(x, 1.0f), xa(x, 1.0f)); }
+        } else {
+            if (ix < 0x401c0000) { id = 2; x = xd(xs(x, 1.5f), xa(1.0f, xm(1.5f, x))); }
+            else { id = 3; x = xd(-1.0f, x); }
+        }
+    }
+    const float z = xm(x, x), w = xm(z, z);
+    const float s1 = xm(z, xa(3.3333334327e-01f, xm(w, xa(1.4285714924e-01f, xm(w, xa(9.0908870101e-02f,
+                     xm(w, xa(6.6610731184e-02f, xm(w, xa(4.9768779427e-02f, xm(w, 1.6285819933e-02f)))))))))));
+    const float s2 = xm(w, xa(-2.0000000298e-01f, xm(w, xa(-1.1111110449e-01f, xm(w, xa(-7.6918758452e-02f,
+                     xm(w, xa(-5.8335702866e-02f, xm(w, -3.6531571299e-02f)))))))));
+    if (id < 0) return xs(x, xm(x, xa(s1, s2)));
+    const float h = id == 0 ? hi[0] : (id == 1 ? hi[1] : (id == 2 ? hi[2] : hi[3]));
+    const float l = id == 0 ? lo[0] : (id == 1 ? lo[1] : (id == 2 ? lo[2] : lo[3]));
+    const float r = xs(h, xs(xs(xm(x, xa(s1, s2)), l), x));
+    return hx < 0 ? -r : r;
+}
+
 }  // namespace rtb

@@ -302,7 +302,7 @@ static int pack_instance(rtb_context* c, const rtb_instance& in, float4 rec[INST
             mag = std::max(mag, std::fabs(w));
         }
     }
-    if (mi.num_triangles == 0) { for (int a = 0; a < 3; a++) { wlo[a] = 1e30; whi[a] = -1e30; } mag = 0; }
+    if (mi.num_triangles == 0) { for (int a = 0; a < 3; a++) wlo[a] = whi[a] = (&in.pose.x)[a]; mag = 0; }   // empty BLAS: a point
     const double pad = 1e-4 * mag + 1e-5;
     for (int a = 0; a < 3; a++) { lo[a] = (float)(wlo[a] - pad); hi[a] = (float)(whi[a] + pad); }
     return RTB_OK;
@@ -489,6 +489,30 @@ int rtb_frame_stats_get(rtb_context* c, rtb_frame_stats* out)
     out->rays = h.rays; out->nodes_visited = h.nodes; out->tris_tested = h.tris; out->device_ms = c->last_ms; out->overflow = h.overflow;
     out->launches = c->last_launches;
     if (h.overflow) return fail(RTB_ERR_OVERFLOW, "render: traversal stack / ray queue overflow");
+    return RTB_OK;
+}
+
+// ------------------------------------------------------------------ device-math inspection (tests)
+}  // extern "C"
+__global__ void k_debug_math(int what, const float* __restrict__ in, float* __restrict__ out, int n)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (what == 0) out[i] = rtb::xatanf(in[i]);
+    else if (what == 1) out[i] = rtb::q_rsqrt(in[i]);
+}
+extern "C" {
+int rtb_debug_math(rtb_context* c, int what, const float* in_host, float* out_host, int n)
+{
+    if (!c || !in_host || !out_host || n <= 0 || what < 0 || what > 1) return fail(RTB_ERR_INVALID, "rtb_debug_math: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    float *di = nullptr, *dout = nullptr;
+    CU(cudaMalloc((void**)&di, sizeof(float) * (size_t)n), "cudaMalloc");
+    CU(cudaMalloc((void**)&dout, sizeof(float) * (size_t)n), "cudaMalloc");
+    CU(cudaMemcpy(di, in_host, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice), "copy");
+    k_debug_math<<<(n + 255) / 256, 256>>>(what, di, dout, n);
+    CU(cudaMemcpy(out_host, dout, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost), "copy");
+    cudaFree(di); cudaFree(dout);
     return RTB_OK;
 }
 

@@ -204,7 +204,7 @@ __global__ void k_fit(const float4* __restrict__ bmin, const float4* __restrict_
         int cnt = rg.y - rg.x + 1;
         float c_split = c_node * h + lb.w + rb.w;
         float c_leaf = cnt <= max_leaf ? c_tri * h * (float)cnt : FLT_MAX;
-        bool leaf = c_leaf <= c_split;
+        bool leaf = cnt <= max_leaf && !(c_leaf > c_split);   // never a leaf above max_leaf, whatever the costs (inf/NaN boxes)
         mn.w = h; mx.w = leaf ? c_leaf : c_split;
         nb_min[cur] = mn; nb_max[cur] = mx;
         flags[cur] = leaf ? 1 : 0;

@@ -14,7 +14,7 @@ XF f3 generate_direction(const FrameParams& P, float px, float py)
     float dz = xa(xa(xm(K[6], px), xm(K[7], py)), xm(K[8], 1.0f));
     const float a = dx, b = dy;
     const float radius = __fsqrt_rn(xa(xm(a, a), xm(b, b)));
-    const float theta = atanf(radius);
+    const float theta = xatanf(radius);                              // raycast.cu:170, host-libm bits (exact.cuh)
     // raycast.cu:172: float products, summed in double because of the `1.0` literal
     const double s = (((1.0 + (double)xm(P.D[0], theta)) + (double)xm(xm(P.D[1], theta), theta)) +
                       (double)xm(xm(xm(P.D[2], theta), theta), theta)) +

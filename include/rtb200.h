@@ -129,6 +129,9 @@ RTB_API int rtb_render_host(rtb_context* ctx, const rtb_render_params* p, unsign
                             const rtb_aovs* aovs_host);
 RTB_API int rtb_synchronize(rtb_context* ctx);                                            /* cudaDeviceSynchronize, kernel.cu:279 */
 RTB_API int rtb_frame_stats_get(rtb_context* ctx, rtb_frame_stats* out);
+/* Evaluates a device math helper on n host floats (tests): what = 0 atanf with host-libm bits (raycast.cu:170),
+ * 1 Q_rsqrt (utils.hpp:12-27). */
+RTB_API int rtb_debug_math(rtb_context* ctx, int what, const float* in_host, float* out_host, int n);
 
 /* ---- host helpers with reference-exact arithmetic (kernel inputs must be bit-compatible) ------- */
 RTB_API void rtb_invert_intrinsic(const float K[9], float K_inv[9]);      /* utils.hpp:142-160      */

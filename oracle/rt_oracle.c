@@ -61,6 +61,9 @@ void o_invert_intrinsic(const float K[9], float Ki[9])
     Ki[6] = 0.0f; Ki[7] = 0.0f; Ki[8] = 1.0f;
 }
 
+/* the libm calls of the path, exposed so device-side restatements can be checked against them */
+void o_libm_atanf(const float* in, float* out, int n) { for (int i = 0; i < n; i++) out[i] = atanf(in[i]); }
+
 /* ------------------------------------------------------------------ transforms.hpp */
 
 typedef struct { float m[3][3]; } m33;

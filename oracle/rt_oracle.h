@@ -89,6 +89,7 @@ typedef struct {            /* per-frame work counters (for the bounded cpu_base
 
 /* ---- math (utils.hpp / transforms.hpp) ---- */
 float o_Q_rsqrt(float number);
+void o_libm_atanf(const float* in, float* out, int n);   /* libm atanf as called at raycast.cu:170 */
 o_f3 o_normalize(o_f3 v);
 o_f3 o_apply_euler(o_f3 euler, o_f3 v);
 o_f3 o_apply_lre(o_lre l, o_f3 v);
