@@ -355,6 +355,13 @@ int rtb_update_instance(rtb_context* c, int index, const rtb_instance* inst)
 }
 
 // ------------------------------------------------------------------ render
+static float bounds_extent(const float b[6], int n)
+{
+    float e = 0.f;
+    if (n > 0) for (int k = 0; k < 6; k++) e = std::max(e, std::fabs(b[k]));
+    return e;
+}
+
 static int make_scene(rtb_context* c, SceneDev& sc)
 {
     if (!c->tlas.nodes) return fail(RTB_ERR_STATE, "render: no instances set (call rtb_set_instances)");
@@ -369,7 +376,7 @@ static int make_scene(rtb_context* c, SceneDev& sc)
         std::vector<MeshDev> t(cap);
         for (int i = 0; i < n; i++) {
             const MeshRec& m = c->meshes[i];
-            t[i].nodes = m.bvh.nodes; t[i].tris = m.tri_rec; t[i].uvs = m.uvs; t[i].num_triangles = m.n; t[i].pad = 0;
+            t[i].nodes = m.bvh.nodes; t[i].tris = m.tri_rec; t[i].uvs = m.uvs; t[i].num_triangles = m.n; t[i].extent = bounds_extent(m.bvh.bounds, m.n);
         }
         CU(cudaMemcpy(c->meshes_d, t.data(), sizeof(MeshDev) * (size_t)cap, cudaMemcpyHostToDevice), "mesh table upload");
         c->mesh_table_dirty = false;
@@ -378,6 +385,7 @@ static int make_scene(rtb_context* c, SceneDev& sc)
         if (!c->meshes[in.mesh_index].alive) return fail(RTB_ERR_STATE, "render: an instance refers to a destroyed mesh");
     sc.tlas_nodes = c->tlas.nodes; sc.tlas_index = (const int*)c->tlas.order; sc.inst = c->inst_d; sc.meshes = c->meshes_d;
     sc.materials = c->materials_d; sc.num_instances = (int)c->instances_h.size(); sc.num_materials = (int)c->materials_h.size();
+    sc.tlas_extent = bounds_extent(c->tlas.bounds, sc.num_instances);
     return RTB_OK;
 }
 

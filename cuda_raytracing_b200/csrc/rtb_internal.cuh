@@ -37,7 +37,7 @@ struct MeshDev {
     const float4* tris;             // triangle records in leaf order
     const float2* uvs;              // 3 x float2 per ORIGINAL triangle index (TrianglePrimitive::uv_coords)
     int num_triangles;
-    int pad;
+    float extent;                   // largest |coordinate| of the mesh bounds (slab-test error bound)
 };
 
 struct SceneDev {
@@ -48,6 +48,7 @@ struct SceneDev {
     const rtb_material* materials;
     int num_instances;
     int num_materials;
+    float tlas_extent;              // largest |coordinate| of any instance world box
 };
 
 struct FrameParams {
