@@ -1,0 +1,4 @@
+// BVHTree.hpp -- forwarding header: keeps `#include "BVHTree.hpp"` of code written against AFIDclan/cuda-raytracing compiling.
+// The whole drop-in surface lives in raytracer.hpp.
+#pragma once
+#include "raytracer.hpp"

@@ -1,0 +1,4 @@
+// MeshInstance.hpp -- forwarding header: keeps `#include "MeshInstance.hpp"` of code written against AFIDclan/cuda-raytracing compiling.
+// The whole drop-in surface lives in raytracer.hpp.
+#pragma once
+#include "raytracer.hpp"

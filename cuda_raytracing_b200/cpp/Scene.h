@@ -1,0 +1,4 @@
+// Scene.h -- forwarding header: keeps `#include "Scene.h"` of code written against AFIDclan/cuda-raytracing compiling.
+// The whole drop-in surface lives in raytracer.hpp.
+#pragma once
+#include "raytracer.hpp"

@@ -1,0 +1,4 @@
+// TrianglePrimitive.hpp -- forwarding header: keeps `#include "TrianglePrimitive.hpp"` of code written against AFIDclan/cuda-raytracing compiling.
+// The whole drop-in surface lives in raytracer.hpp.
+#pragma once
+#include "raytracer.hpp"

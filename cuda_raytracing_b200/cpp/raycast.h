@@ -1,0 +1,4 @@
+// raycast.h -- forwarding header: keeps `#include "raycast.h"` of code written against AFIDclan/cuda-raytracing compiling.
+// The whole drop-in surface lives in raytracer.hpp.
+#pragma once
+#include "raytracer.hpp"

@@ -1,0 +1,4 @@
+// transforms.hpp -- forwarding header: keeps `#include "transforms.hpp"` of code written against AFIDclan/cuda-raytracing compiling.
+// The whole drop-in surface lives in raytracer.hpp.
+#pragma once
+#include "raytracer.hpp"

@@ -1,0 +1,4 @@
+// utils.hpp -- forwarding header: keeps `#include "utils.hpp"` of code written against AFIDclan/cuda-raytracing compiling.
+// The whole drop-in surface lives in raytracer.hpp.
+#pragma once
+#include "raytracer.hpp"

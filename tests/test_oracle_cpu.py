@@ -188,6 +188,16 @@ def test_cabi_exports_every_declared_symbol(rtb):
     assert set(rtb.EXPORTS) <= set(declared)
 
 
+def test_cpp_dropin_builds():
+    """The C++ classes with the reference's names compile and link against the C-ABI (kernel.cu-style demo)."""
+    cpp = os.path.join(ROOT, "cuda_raytracing_b200", "cpp")
+    subprocess.check_call(["make", "-C", cpp, "-s"])
+    assert os.path.exists(os.path.join(cpp, "demo"))
+    for h in ("Scene.h", "Camera.h", "MeshInstance.hpp", "Material.hpp", "MeshPrimitive.h", "OBJLoader.hpp", "TrianglePrimitive.hpp",
+              "transforms.hpp", "utils.hpp", "BVHTree.hpp"):
+        assert os.path.exists(os.path.join(cpp, h)), h
+
+
 def test_no_gpu_fails_loudly(rtb):
     """No CPU fallback: without a usable device the context cannot be created."""
     import torch
