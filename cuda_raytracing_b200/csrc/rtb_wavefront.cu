@@ -103,6 +103,26 @@ __global__ void __launch_bounds__(256) k_gen(FrameParams P, int sample, int n_lo
 }
 
 // ------------------------------------------------------------------ stage 1 / 3: queue tracer with lane refill
+// Hit sink of the queue tracer: an accepted candidate goes straight to this ray's hit record in HBM (accepts are
+// rare, ~1-2 per ray), so only what the accept rule compares stays in registers during the traversal.
+template <bool ANY>
+struct QueueSink {
+    float hmin; int hinst, hprim, ray;
+    float4* __restrict__ h0; float4* __restrict__ h1;
+    XF void reset(int r) { hmin = FLT_MAX; hinst = -1; hprim = -1; ray = r; }
+    XF float min() const { return hmin; }
+    XF int inst() const { return hinst; }
+    XF int prim() const { return hprim; }
+    XF void accept(float distance, int slot, int prim, int inst, float u, float v, f3 loc)
+    {
+        hmin = distance; hinst = inst; hprim = prim;
+        if (!ANY) {
+            h0[ray] = make_float4(distance, u, v, __int_as_float(inst));
+            h1[ray] = make_float4(loc.x, loc.y, loc.z, __int_as_float(slot));
+        }
+    }
+};
+
 template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(128) k_trace_queue(SceneDev sc, const float4* __restrict__ q_org, const float4* __restrict__ q_dir,
                                                      float3 cdir, const int* __restrict__ count_ptr, int* __restrict__ head,
@@ -113,21 +133,24 @@ __global__ void __launch_bounds__(128) k_trace_queue(SceneDev sc, const float4* 
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
     const int count = *count_ptr;
+    uint2 stk[STACK_CAP];
     TraceState S;
+    QueueSink<ANY> sink;
+    sink.h0 = hit0; sink.h1 = hit1;
+    sink.reset(-1);
     S.clear();
-    int ray = -1, pix = -1;
+    int pix = -1;
     bool more = true;                           // warp-uniform: the queue may still hold rays
     unsigned rays = 0;
     for (;;) {
         const bool idle = S.cur == EMPTY_REF;
-        if (idle && ray >= 0) {                 // retire the finished ray
+        if (idle && sink.ray >= 0) {            // retire the finished ray
             if (!ANY) {
-                hit0[ray] = make_float4(S.hit.min, S.hit.u, S.hit.v, __int_as_float(S.hit.inst));
-                hit1[ray] = make_float4(S.hit.loc.x, S.hit.loc.y, S.hit.loc.z, __int_as_float(S.hit.slot));
+                if (sink.hmin == FLT_MAX) hit0[sink.ray] = make_float4(FLT_MAX, 0.f, 0.f, __int_as_float(-1));
             } else {
                 // commented block raycast.cu:262-290: illumination = 0.4 cos, or cos when the light is visible; clamp [0.4, 1]
-                const float4 p0 = sp0[ray], p1 = sp1[ray];
-                float il = S.hit.min == FLT_MAX ? p1.w : __double2float_rn(__dmul_rn(0.4, (double)p1.w));
+                const float4 p0 = sp0[sink.ray], p1 = sp1[sink.ray];
+                float il = sink.hmin == FLT_MAX ? p1.w : __double2float_rn(__dmul_rn(0.4, (double)p1.w));
                 il = fmaxf(0.4f, fminf(1.0f, il));
                 float4 a = acc[pix];
                 a.x = xa(a.x, xm(p0.x, xm(p0.w, xm(il, p1.x))));
@@ -135,7 +158,7 @@ __global__ void __launch_bounds__(128) k_trace_queue(SceneDev sc, const float4* 
                 a.z = xa(a.z, xm(p0.z, xm(p0.w, xm(il, p1.z))));
                 acc[pix] = a;
             }
-            ray = -1;
+            sink.ray = -1;
         }
         const unsigned im = __ballot_sync(0xffffffffu, idle);
         if (more && im) {                       // refill idle lanes: one atomic per warp
@@ -152,8 +175,8 @@ __global__ void __launch_bounds__(128) k_trace_queue(SceneDev sc, const float4* 
                         f3 d;
                         if (ANY) d = mk3(cdir.x, cdir.y, cdir.z);
                         else { const float4 dd = q_dir[i]; d = mk3(dd.x, dd.y, dd.z); }
-                        ray = i;
-                        S.begin(sc, mk3(o.x, o.y, o.z), d);
+                        sink.reset(i);
+                        S.begin(sc, mk3(o.x, o.y, o.z), d, stk);
                         rays++;
                     }
                 }
@@ -166,7 +189,7 @@ __global__ void __launch_bounds__(128) k_trace_queue(SceneDev sc, const float4* 
         }
         const int keep = more ? 32 - REFILL_IDLE : 0;   // leave the loop to refill once REFILL_IDLE lanes are idle
         do {
-            S.template advance<ANY, COUNT>(sc);
+            S.template advance<ANY, COUNT>(sc, stk, sink);
         } while (__popc(__ballot_sync(0xffffffffu, S.cur != EMPTY_REF)) > keep);
     }
     S.template flush_counters<COUNT>(ctr);
