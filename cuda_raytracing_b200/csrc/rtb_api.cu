@@ -128,6 +128,9 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     if (n == "counters") c->opt_counters = value;
     else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
     else if (n == "key_bits") c->opt_key_bits = value;
+    else if (n == "trace_minb") rtb::g_tune.trace_minb = value;
+    else if (n == "direct_minb") rtb::g_tune.direct_minb = value;
+    else if (n == "refill_idle") rtb::g_tune.refill_idle = std::max(1, std::min(value, 32));
     else return fail(RTB_ERR_INVALID, "rtb_set_option: unknown option " + n);
     return RTB_OK;
 }

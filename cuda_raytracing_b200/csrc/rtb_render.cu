@@ -8,6 +8,8 @@
 
 namespace rtb {
 
+Tune g_tune;
+
 XF void write_pixel(unsigned char* img, size_t pitch, int x, int y, unsigned char b, unsigned char g, unsigned char r)
 {
     unsigned char* p = img + (size_t)y * pitch + 3 * (size_t)x;
@@ -15,8 +17,8 @@ XF void write_pixel(unsigned char* img, size_t pitch, int x, int y, unsigned cha
 }
 
 // modes RTB_MODE_REFERENCE / RTB_MODE_SHADOW: everything for one pixel in one thread
-template <bool LIT, bool COUNT>
-__global__ void __launch_bounds__(128) k_render_direct(SceneDev sc, FrameParams P, unsigned char* __restrict__ img, size_t pitch,
+template <bool LIT, bool COUNT, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_render_direct(SceneDev sc, FrameParams P, unsigned char* __restrict__ img, size_t pitch,
                                                       int32_t* __restrict__ aov_prim, int32_t* __restrict__ aov_inst,
                                                       float* __restrict__ aov_t, Counters* ctr)
 {
@@ -25,24 +27,31 @@ __global__ void __launch_bounds__(128) k_render_direct(SceneDev sc, FrameParams 
     const int band = blockIdx.y * P.tile_count + P.tile_rank;
     const int y = band * BAND_ROWS + (warp >> 1) * 4 + (lane >> 3);
     unsigned rays = 0;
-    if (x < P.width && y < P.height) {
-        const f3 origin = mk3(P.ox, P.oy, P.oz);
-        const f3 dir = generate_direction(P, (float)x, (float)y);
-        Hit h;
-        trace<false, COUNT>(sc, origin, dir, h, ctr);
-        rays = 1;
+    const bool valid = x < P.width && y < P.height;                                // the whole warp stays: trace() is warp-collective
+    const f3 origin = mk3(P.ox, P.oy, P.oz);
+    f3 dir = mk3(0.f, 0.f, 1.f);
+    if (valid) dir = generate_direction(P, (float)x, (float)y);
+    Hit h;
+    trace<false, COUNT>(sc, valid, origin, dir, h, ctr);
+    const bool is_hit = valid && h.min != FLT_MAX;
+    InstXf xf;
+    f3 c = mk3(0.f, 0.f, 0.f), nrm = mk3(0.f, 0.f, 1.f);
+    if (is_hit) {
+        load_instance(sc.inst, h.inst, xf);
+        c = base_colour(sc, h, xf.material, xf.mesh);
+        if (LIT) nrm = world_normal(sc, h, xf);
+    }
+    float illum = 1.0f;                                                            // raycast.cu:282
+    if (LIT) illum = lit_illumination<COUNT>(sc, P, is_hit, h, nrm, ctr, rays);
+    if (valid) {
+        rays++;
         const size_t pi = (size_t)y * P.width + x;
         if (aov_prim) aov_prim[pi] = h.prim;
         if (aov_inst) aov_inst[pi] = h.inst;
         if (aov_t) aov_t[pi] = h.min;
-        if (h.min == FLT_MAX) {
+        if (!is_hit) {
             write_pixel(img, pitch, x, y, 255, 204, 153);                         // raycast.cu:208-216
         } else {
-            InstXf xf;
-            load_instance(sc.inst, h.inst, xf);
-            const f3 c = base_colour(sc, h, xf.material, xf.mesh);
-            float illum = 1.0f;                                                    // raycast.cu:282
-            if (LIT) illum = lit_illumination<COUNT>(sc, P, h, world_normal(sc, h, xf), ctr, rays);
             illum = fmaxf(0.4f, fminf(1.0f, illum));
             write_pixel(img, pitch, x, y, to_u8(xm(xm(illum, c.x), 255.0f)), to_u8(xm(xm(illum, c.y), 255.0f)),
                         to_u8(xm(xm(illum, c.z), 255.0f)));                       // raycast.cu:292-294
@@ -59,15 +68,16 @@ cudaError_t launch_render(const SceneDev& sc, const FrameParams& P, unsigned cha
     const int my_bands = (bands - P.tile_rank + P.tile_count - 1) / P.tile_count;
     if (my_bands <= 0 || P.width <= 0) return cudaSuccess;
     dim3 grid((P.width + 15) / 16, my_bands);
-    if (P.mode == RTB_MODE_REFERENCE) {
-        if (count) k_render_direct<false, true><<<grid, 128, 0, st>>>(sc, P, img, pitch, aov.prim, aov.inst, aov.t, ctr);
-        else k_render_direct<false, false><<<grid, 128, 0, st>>>(sc, P, img, pitch, aov.prim, aov.inst, aov.t, ctr);
-    } else if (P.mode == RTB_MODE_SHADOW) {
-        if (count) k_render_direct<true, true><<<grid, 128, 0, st>>>(sc, P, img, pitch, aov.prim, aov.inst, aov.t, ctr);
-        else k_render_direct<true, false><<<grid, 128, 0, st>>>(sc, P, img, pitch, aov.prim, aov.inst, aov.t, ctr);
-    } else {
-        return cudaErrorNotSupported;
+    if (P.mode != RTB_MODE_REFERENCE && P.mode != RTB_MODE_SHADOW) return cudaErrorNotSupported;
+    const bool lit = P.mode == RTB_MODE_SHADOW;
+#define RTB_DIRECT(LIT, COUNT, MINB) k_render_direct<LIT, COUNT, MINB><<<grid, 128, 0, st>>>(sc, P, img, pitch, aov.prim, aov.inst, aov.t, ctr)
+    if (count) { if (lit) RTB_DIRECT(true, true, 4); else RTB_DIRECT(false, true, 4); }
+    else {
+        const int mb = g_tune.direct_minb;
+        if (lit) { if (mb <= 4) RTB_DIRECT(true, false, 4); else if (mb == 5) RTB_DIRECT(true, false, 5); else if (mb == 6) RTB_DIRECT(true, false, 6); else RTB_DIRECT(true, false, 8); }
+        else { if (mb <= 4) RTB_DIRECT(false, false, 4); else if (mb == 5) RTB_DIRECT(false, false, 5); else if (mb == 6) RTB_DIRECT(false, false, 6); else RTB_DIRECT(false, false, 8); }
     }
+#undef RTB_DIRECT
     return cudaGetLastError();
 }
 

@@ -4,6 +4,14 @@
 
 namespace rtb {
 
+// Tuning knobs (rtb_set_option "trace_minb" / "direct_minb" / "refill_idle"); process-wide, read at launch time.
+struct Tune {
+    int trace_minb = 8;     // __launch_bounds__(128, N) variant of the queue tracer: resident blocks per SM the registers allow
+    int direct_minb = 6;    // same for the direct kernel
+    int refill_idle = 16;   // queue tracer: refill a warp once this many lanes are idle
+};
+extern Tune g_tune;
+
 cudaError_t launch_render(const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch, const rtb_aovs& aov,
                           Counters* ctr, bool count, cudaStream_t st);
 

@@ -63,17 +63,19 @@ XF unsigned char to_u8(float v) { return (unsigned char)__float2int_rz(v); }   /
 XF float clamp01(float v) { return fminf(1.0f, fmaxf(0.0f, v)); }
 
 // Lambert + shadow term of the commented block raycast.cu:262-280 with the live light setup 249-259.
-// Returns the clamped illumination (289-290); *shadow_rays counts the any-hit ray if one was cast.
+// Returns the clamped illumination (289-290); counts the any-hit ray if one was cast.  Warp-collective: every
+// lane calls it, lanes without a hit pass lit=false.
 template <bool COUNT>
-XF float lit_illumination(const SceneDev& sc, const FrameParams& P, const Hit& h, f3 nrm, Counters* ctr, unsigned& rays)
+XF float lit_illumination(const SceneDev& sc, const FrameParams& P, bool lit, const Hit& h, f3 nrm, Counters* ctr, unsigned& rays)
 {
     const f3 L = mk3(P.light_dir.x, P.light_dir.y, P.light_dir.z);
-    const float cos_illum = xdot(nrm, L);
+    const float cos_illum = lit ? xdot(nrm, L) : 0.0f;
     float illum = __double2float_rn(__dmul_rn(0.4, (double)cos_illum));
-    if (cos_illum > 0.0f) {
-        const f3 so = xadd(h.loc, xscale(L, 1e-4f));                   // raycast.cu:259
-        Hit sh;
-        trace<true, COUNT>(sc, so, L, sh, ctr);
+    const bool cast = lit && cos_illum > 0.0f;
+    const f3 so = xadd(h.loc, xscale(L, 1e-4f));                       // raycast.cu:259
+    Hit sh;
+    trace<true, COUNT>(sc, cast, so, L, sh, ctr);
+    if (cast) {
         rays++;
         if (sh.min == FLT_MAX) illum = cos_illum;
     }

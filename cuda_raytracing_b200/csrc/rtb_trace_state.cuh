@@ -116,21 +116,25 @@ struct TraceState {
             const int s0 = k[0] & 3;
             cur = s0 == 0 ? rr[0] : (s0 == 1 ? rr[1] : (s0 == 2 ? rr[2] : rr[3]));
         }
-        if (cur == EMPTY_REF) return;
-        if (cur == LEAVE_REF) {                 // instance exhausted: back to world space
-            in_blas = false; nodes = sc.tlas_nodes;
-            cur = pop(stk);
-            if (cur >= 0) { r.o = org; r.d = dir; setup_slabs(r); return; }
-            if (cur == EMPTY_REF) return;
-        }
-        // leaf
-        const unsigned bits = ~(unsigned)cur;
-        const int first = (int)(bits >> 3), count = (int)(bits & 7u) + 1;
-        if (!in_blas) {                         // TLAS leaf: exactly one instance slot
-            if (sp + 1 > STACK_CAP) { overflow = true; cur = EMPTY_REF; return; }
-            enter_instance(sc, __ldg(sc.tlas_index + first), stk, true);
+        // Reconvergence point: every lane of the warp calls advance() (both drivers guarantee it), and without this
+        // barrier lanes leave the interior loop in small groups and run the leaf code 2 lanes wide (ncu, profiles/r01b).
+        __syncwarp();
+        const bool tri_leaf = in_blas && cur < 0 && cur != EMPTY_REF && cur != LEAVE_REF;
+        if (!tri_leaf) {
+            if (cur == LEAVE_REF) {             // instance exhausted: back to world space
+                in_blas = false; nodes = sc.tlas_nodes;
+                cur = pop(stk);
+                if (cur >= 0) { r.o = org; r.d = dir; setup_slabs(r); }
+            }
+            if (cur < 0 && cur != EMPTY_REF) {  // TLAS leaf: exactly one instance slot
+                const int first = (int)((~(unsigned)cur) >> 3);
+                if (sp + 1 > STACK_CAP) { overflow = true; cur = EMPTY_REF; return; }
+                enter_instance(sc, __ldg(sc.tlas_index + first), stk, true);
+            }
             return;
         }
+        const unsigned bits = ~(unsigned)cur;
+        const int first = (int)(bits >> 3), count = (int)(bits & 7u) + 1;
         bool found = false;
         for (int i = 0; i < count; i++) {
             const float4* q = tris + (size_t)(first + i) * TRI_F4;
@@ -189,16 +193,17 @@ struct TraceState {
 
 // Closest hit (ANY=false) or any hit (ANY=true; stops at the first accepted candidate, the commented
 // lighting_pass early-out of raycast.cu:128-132) for one ray.
+// Must be called by all 32 lanes of the warp (advance() holds a warp barrier); lanes without a ray pass active=false.
 template <bool ANY, bool COUNT>
-__device__ __forceinline__ void trace(const SceneDev& sc, f3 org, f3 dir, Hit& hit, Counters* ctr)
+__device__ __forceinline__ void trace(const SceneDev& sc, bool active, f3 org, f3 dir, Hit& hit, Counters* ctr)
 {
     uint2 stk[STACK_CAP];
     TraceState S;
     RegSink sink;
     sink.reset();
     S.clear();
-    S.begin(sc, org, dir, stk);
-    while (S.cur != EMPTY_REF) S.template advance<ANY, COUNT>(sc, stk, sink);
+    if (active) S.begin(sc, org, dir, stk);
+    while (__any_sync(0xffffffffu, S.cur != EMPTY_REF)) S.template advance<ANY, COUNT>(sc, stk, sink);
     S.template flush_counters<COUNT>(ctr);
     hit = sink.hit;
 }

@@ -21,7 +21,6 @@ struct rtb_context;
 
 namespace rtb {
 
-constexpr int REFILL_IDLE = 8;      // refill a warp from the queue once this many lanes are idle
 
 struct WaveState {
     float4* q_org[2] = { nullptr, nullptr };
@@ -123,8 +122,8 @@ struct QueueSink {
     }
 };
 
-template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(128) k_trace_queue(SceneDev sc, const float4* __restrict__ q_org, const float4* __restrict__ q_dir,
+template <bool ANY, bool COUNT, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_trace_queue(int refill_idle, SceneDev sc, const float4* __restrict__ q_org, const float4* __restrict__ q_dir,
                                                      float3 cdir, const int* __restrict__ count_ptr, int* __restrict__ head,
                                                      float4* __restrict__ hit0, float4* __restrict__ hit1,
                                                      const float4* __restrict__ sp0, const float4* __restrict__ sp1,
@@ -187,7 +186,7 @@ __global__ void __launch_bounds__(128) k_trace_queue(SceneDev sc, const float4* 
             if (!more) break;
             continue;
         }
-        const int keep = more ? 32 - REFILL_IDLE : 0;   // leave the loop to refill once REFILL_IDLE lanes are idle
+        const int keep = more ? 32 - refill_idle : 0;   // leave the loop to refill once refill_idle lanes are idle
         do {
             S.template advance<ANY, COUNT>(sc, stk, sink);
         } while (__popc(__ballot_sync(0xffffffffu, S.cur != EMPTY_REF)) > keep);
@@ -361,13 +360,9 @@ cudaError_t launch_wavefront(rtb_context*, void** state, const SceneDev& sc, con
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    static int occ_closest = 0, occ_any = 0;
-    if (!occ_closest) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_closest, k_trace_queue<false, false>, 128, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_any, k_trace_queue<true, false>, 128, 0);
-        occ_closest = std::max(1, occ_closest); occ_any = std::max(1, occ_any);
-    }
-    const int grid_t = sms * occ_closest, grid_s = sms * occ_any;
+    const int mb = g_tune.trace_minb <= 4 ? 4 : (g_tune.trace_minb == 5 ? 5 : (g_tune.trace_minb == 6 ? 6 : 8));
+    const int ri = g_tune.refill_idle;
+    const int grid_t = sms * (count ? 4 : mb), grid_s = grid_t;
     const int grid_shade = std::min(sms * 8, (n_local + 127) / 128);
     const float3 L = P.light_dir;
     g_wave_launches = 0;
@@ -383,14 +378,16 @@ cudaError_t launch_wavefront(rtb_context*, void** state, const SceneDev& sc, con
         g_wave_launches++;
         for (int b = 0; b <= P.max_depth; b++) {
             int* c4 = c0 + 4 * b;
-            if (count) k_trace_queue<false, true><<<grid_t, 128, 0, st>>>(sc, w->q_org[b & 1], w->q_dir[b & 1], L, c4 + 0, c4 + 1, w->hit0, w->hit1, nullptr, nullptr, nullptr, ctr);
-            else k_trace_queue<false, false><<<grid_t, 128, 0, st>>>(sc, w->q_org[b & 1], w->q_dir[b & 1], L, c4 + 0, c4 + 1, w->hit0, w->hit1, nullptr, nullptr, nullptr, ctr);
+#define RTB_TQ(ANY, COUNT, MINB, GRID, ...) k_trace_queue<ANY, COUNT, MINB><<<GRID, 128, 0, st>>>(ri, sc, __VA_ARGS__)
+#define RTB_TQ_MB(ANY, GRID, ...) do { if (count) RTB_TQ(ANY, true, 4, GRID, __VA_ARGS__); else if (mb == 4) RTB_TQ(ANY, false, 4, GRID, __VA_ARGS__); \
+            else if (mb == 5) RTB_TQ(ANY, false, 5, GRID, __VA_ARGS__); else if (mb == 6) RTB_TQ(ANY, false, 6, GRID, __VA_ARGS__); \
+            else RTB_TQ(ANY, false, 8, GRID, __VA_ARGS__); } while (0)
+            RTB_TQ_MB(false, grid_t, w->q_org[b & 1], w->q_dir[b & 1], L, c4 + 0, c4 + 1, w->hit0, w->hit1, nullptr, nullptr, nullptr, ctr);
             if (path) k_shade<true><<<grid_shade, 128, 0, st>>>(sc, P, b, s, *w, c4, aov.prim, aov.inst, aov.t);
             else k_shade<false><<<grid_shade, 128, 0, st>>>(sc, P, b, s, *w, c4, aov.prim, aov.inst, aov.t);
             g_wave_launches += 2;
             if (!path) {
-                if (count) k_trace_queue<true, true><<<grid_s, 128, 0, st>>>(sc, w->s_org, nullptr, L, c4 + 2, c4 + 3, nullptr, nullptr, w->s_p0, w->s_p1, w->acc, ctr);
-                else k_trace_queue<true, false><<<grid_s, 128, 0, st>>>(sc, w->s_org, nullptr, L, c4 + 2, c4 + 3, nullptr, nullptr, w->s_p0, w->s_p1, w->acc, ctr);
+                RTB_TQ_MB(true, grid_s, w->s_org, nullptr, L, c4 + 2, c4 + 3, nullptr, nullptr, w->s_p0, w->s_p1, w->acc, ctr);
                 g_wave_launches++;
             }
         }

@@ -1,0 +1,54 @@
+#!/usr/bin/env python
+"""Knob sweep on a GPU box: frame ms of a bench config for each setting of the launch-bounds / refill knobs.
+   python tools/tune.py c3 trace_minb=4,5,6,8 refill_idle=4,8,16     (cartesian product; CUDA events, L2 flushed)"""
+import itertools, os, sys, json
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import bench
+from cuda_raytracing_b200 import api
+
+def main():
+    name = sys.argv[1]
+    knobs = [(a.split("=")[0], [int(v) for v in a.split("=")[1].split(",")]) for a in sys.argv[2:]]
+    cfg = bench.CONFIGS[name]
+    W, H = cfg["w"], cfg["h"]
+    K, D = bench.config_K(cfg)
+    tris = bench.build_tris(cfg)
+    scene = api.Scene(0)
+    for m in bench.scene_materials(cfg):
+        scene.add_material(api.Material(albedo=m["albedo"], metallic=m["metallic"]))
+    scene.add_mesh(api.MeshPrimitive(tris))
+    for (mi, ma, pose, scale) in bench.scene_instances(cfg):
+        scene.add_mesh_instance(api.MeshInstance(mi, ma, pose, scale))
+    scene.upload_to_device()
+    cam = api.Camera(W, H, K, D)
+    cam.mode, cam.max_depth, cam.spp = cfg["mode"], cfg["depth"], min(cfg["spp"], 2)
+    frame = torch.zeros((H, W * 3), dtype=torch.uint8, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    ref = None
+    for combo in itertools.product(*[v for _, v in knobs]):
+        for (k, _), v in zip(knobs, combo):
+            scene.set_option(k, v)
+        ms = []
+        for i in range(7):
+            cam.pose = np.array(bench.camera_pose(cfg, i), np.float32)
+            flush.fill_(i)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            cam.render_scene(scene, frame.data_ptr(), W * 3)
+            e1.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                ms.append(e0.elapsed_time(e1))
+        h = int(frame.to(torch.int64).sum().item())
+        if ref is None:
+            ref = h
+        rays = scene.frame_stats()["rays"]
+        print(json.dumps(dict(config=name, knobs=dict(zip([k for k, _ in knobs], combo)), ms=round(float(np.mean(ms)), 3), ms_min=round(min(ms), 3),
+                              mrays=round(rays / np.mean(ms) / 1e3, 1), same_image=(h == ref))), flush=True)
+    scene.close()
+
+if __name__ == "__main__":
+    main()
