@@ -7,8 +7,8 @@ namespace rtb {
 // Tuning knobs (rtb_set_option "trace_minb" / "direct_minb" / "refill_idle"); process-wide, read at launch time.
 struct Tune {
     int trace_minb = 8;     // __launch_bounds__(128, N) variant of the queue tracer: resident blocks per SM the registers allow
-    int direct_minb = 6;    // same for the direct kernel
-    int refill_idle = 16;   // queue tracer: refill a warp once this many lanes are idle
+    int direct_minb = 8;    // same for the direct kernel
+    int refill_idle = 28;   // queue tracer: refill a warp once this many lanes are idle
 };
 extern Tune g_tune;
 

@@ -55,14 +55,13 @@ XF void test_node(const float4* __restrict__ node, const InstRay& r, float tmax,
     const float ax[4] = { nxv.x, nxv.y, nxv.z, nxv.w }, bx[4] = { fxv.x, fxv.y, fxv.z, fxv.w };
     const float ay[4] = { nyv.x, nyv.y, nyv.z, nyv.w }, by[4] = { fyv.x, fyv.y, fyv.z, fyv.w };
     const float az[4] = { nzv.x, nzv.y, nzv.z, nzv.w }, bz[4] = { fzv.x, fzv.y, fzv.z, fzv.w };
-    const int rfi[4] = { refs.x, refs.y, refs.z, refs.w };
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         const float tnx = fmaf(ax[i], r.idnx, -r.oinx), tny = fmaf(ay[i], r.idny, -r.oiny), tnz = fmaf(az[i], r.idnz, -r.oinz);
         const float tfx = fmaf(bx[i], r.idfx, -r.oifx), tfy = fmaf(by[i], r.idfy, -r.oify), tfz = fmaf(bz[i], r.idfz, -r.oifz);
         const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
         const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-        const bool hit = (tn <= tf) && (rfi[i] != EMPTY_REF);
+        const bool hit = tn <= tf;        // empty slots hold (+inf, +inf) boxes: tn = +inf or tf = -inf, never a hit
         keys[i] = hit ? ((__float_as_uint(tn) & ~3u) | (unsigned)i) : 0xffffffffu;
     }
 }

@@ -93,52 +93,57 @@ struct TraceState {
         return EMPTY_REF;
     }
 
+    // ref of the child in slot s (0..3) of a node, branch-free (three selects)
+    static XF int sel4(unsigned s, const int4& r)
+    {
+        const int lo = (s & 1u) ? r.y : r.x, hi = (s & 1u) ? r.w : r.z;
+        return (s & 2u) ? hi : lo;
+    }
+    static XF bool is_leaf_ref(int ref) { return (unsigned)ref > (unsigned)LEAVE_REF; }   // negative, not EMPTY / LEAVE
+
     template <bool ANY, bool COUNT, class Sink>
     XF void advance(const SceneDev& sc, uint2* __restrict__ stk, Sink& sink)
     {
+        if (++guard > (1u << 22)) { overflow = true; cur = EMPTY_REF; }   // a frame can never hang the device
+        // Speculative traversal: the first triangle leaf a lane meets is postponed (`pend`) and the lane keeps walking
+        // interior nodes, so it does useful work while the slower lanes of the warp are still descending; the loop
+        // ends for the warp when every lane still in it holds a postponed leaf.
+        int pend = EMPTY_REF;
         while (cur >= 0) {                      // interior nodes
-            if (++guard > (1u << 22)) { overflow = true; cur = EMPTY_REF; break; }   // a frame can never hang the device
             unsigned k[4]; int4 refs;
             if (COUNT) n_nodes++;
+            if (sp + 3 > STACK_CAP) { overflow = true; cur = EMPTY_REF; break; }
             test_node(nodes + (size_t)cur * NODE_F4, r, tmax, k, refs);
             RTB_CSWAP(k[0], k[1]); RTB_CSWAP(k[2], k[3]); RTB_CSWAP(k[0], k[2]); RTB_CSWAP(k[1], k[3]); RTB_CSWAP(k[1], k[2]);
-            if (k[0] == 0xffffffffu) { cur = pop(stk); continue; }
-            const int rr[4] = { refs.x, refs.y, refs.z, refs.w };
-            if (sp + 3 > STACK_CAP) { overflow = true; cur = EMPTY_REF; break; }
-#pragma unroll
-            for (int i = 3; i >= 1; i--) {      // far first, so the nearer children are popped first
-                if (k[i] != 0xffffffffu) {
-                    const int s = k[i] & 3;
-                    const int cref = s == 0 ? rr[0] : (s == 1 ? rr[1] : (s == 2 ? rr[2] : rr[3]));
-                    stk[sp++] = make_uint2(k[i] & ~3u, (unsigned)cref);
-                }
-            }
-            const int s0 = k[0] & 3;
-            cur = s0 == 0 ? rr[0] : (s0 == 1 ? rr[1] : (s0 == 2 ? rr[2] : rr[3]));
+            const int c0 = sel4(k[0] & 3u, refs), c1 = sel4(k[1] & 3u, refs), c2 = sel4(k[2] & 3u, refs), c3 = sel4(k[3] & 3u, refs);
+            // far first, so the nearer children are popped first (misses sort last: key 0xffffffff)
+            if (k[3] != 0xffffffffu) stk[sp++] = make_uint2(k[3] & ~3u, (unsigned)c3);
+            if (k[2] != 0xffffffffu) stk[sp++] = make_uint2(k[2] & ~3u, (unsigned)c2);
+            if (k[1] != 0xffffffffu) stk[sp++] = make_uint2(k[1] & ~3u, (unsigned)c1);
+            int nxt = c0;
+            if (k[0] == 0xffffffffu) nxt = pop(stk);
+            if (in_blas && pend == EMPTY_REF && is_leaf_ref(nxt)) { pend = nxt; nxt = pop(stk); }
+            cur = nxt;
+            if (!__any_sync(__activemask(), pend == EMPTY_REF)) break;
         }
         // Reconvergence point: every lane of the warp calls advance() (both drivers guarantee it), and without this
         // barrier lanes leave the interior loop in small groups and run the leaf code 2 lanes wide (ncu, profiles/r01b).
         __syncwarp();
-        const bool tri_leaf = in_blas && cur < 0 && cur != EMPTY_REF && cur != LEAVE_REF;
-        if (!tri_leaf) {
-            if (cur == LEAVE_REF) {             // instance exhausted: back to world space
-                in_blas = false; nodes = sc.tlas_nodes;
-                cur = pop(stk);
-                if (cur >= 0) { r.o = org; r.d = dir; setup_slabs(r); }
-            }
-            if (cur < 0 && cur != EMPTY_REF) {  // TLAS leaf: exactly one instance slot
-                const int first = (int)((~(unsigned)cur) >> 3);
-                if (sp + 1 > STACK_CAP) { overflow = true; cur = EMPTY_REF; return; }
-                enter_instance(sc, __ldg(sc.tlas_index + first), stk, true);
-            }
-            return;
+        // triangle phase: the postponed leaf, then the leaf in `cur` (flattened into one loop over triangle slots)
+        const bool cur_leaf = in_blas && is_leaf_ref(cur);
+        int t0 = 0, t1 = 0, u0 = 0, u1 = 0;
+        if (pend != EMPTY_REF) { const unsigned b = ~(unsigned)pend; t0 = (int)(b >> 3); t1 = t0 + (int)(b & 7u) + 1; }
+        if (cur_leaf) {
+            const unsigned b = ~(unsigned)cur;
+            const int f = (int)(b >> 3), e = f + (int)(b & 7u) + 1;
+            if (pend != EMPTY_REF) { u0 = f; u1 = e; } else { t0 = f; t1 = e; }
         }
-        const unsigned bits = ~(unsigned)cur;
-        const int first = (int)(bits >> 3), count = (int)(bits & 7u) + 1;
         bool found = false;
-        for (int i = 0; i < count; i++) {
-            const float4* q = tris + (size_t)(first + i) * TRI_F4;
+        while (t0 < t1) {
+            const int slot = t0;
+            const float4* q = tris + (size_t)slot * TRI_F4;
             const float4 q0 = __ldg(q + 0), q1 = __ldg(q + 1);
+            if (++t0 == t1) { t0 = u0; t1 = u1; u0 = u1 = 0; }
             if (COUNT) n_tris++;
             const f3 n = mk3(q0.x, q0.y, q0.z);
             // TrianglePrimitive.hpp:64-68  denom = dot(ray.direction, normal); |denom| < 1e-6 (double compare) rejects.
@@ -170,13 +175,24 @@ struct TraceState {
             const bool closer = (hmin == FLT_MAX) || (distance < hmin) ||
                                 (distance == hmin && (cur_inst < sink.inst() || (cur_inst == sink.inst() && prim < sink.prim())));
             if (closer) {
-                sink.accept(distance, first + i, prim, cur_inst, u, v, loc);
+                sink.accept(distance, slot, prim, cur_inst, u, v, loc);
                 tmax = fmaf(distance, inv_len, 1e-3f * inv_len);
                 found = true;
             }
         }
         if (ANY && found) { cur = EMPTY_REF; return; }
-        cur = pop(stk);
+        if (cur_leaf) cur = pop(stk);
+        // events: leave the instance (sentinel popped), enter the instance of a TLAS leaf
+        if (cur == LEAVE_REF) {                 // instance exhausted: back to world space
+            in_blas = false; nodes = sc.tlas_nodes;
+            cur = pop(stk);
+            if (cur >= 0) { r.o = org; r.d = dir; setup_slabs(r); }
+        }
+        if (!in_blas && is_leaf_ref(cur)) {     // TLAS leaf: exactly one instance slot
+            const int first = (int)((~(unsigned)cur) >> 3);
+            if (sp + 1 > STACK_CAP) { overflow = true; cur = EMPTY_REF; return; }
+            enter_instance(sc, __ldg(sc.tlas_index + first), stk, true);
+        }
     }
 
     template <bool COUNT>
