@@ -128,6 +128,8 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     if (n == "counters") c->opt_counters = value;
     else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
     else if (n == "key_bits") c->opt_key_bits = value;
+    else if (n == "fused") rtb::g_tune.fused = value;
+    else if (n == "smem_top") rtb::g_tune.smem_top = std::max(0, std::min(value, 341));
     else if (n == "trace_minb") rtb::g_tune.trace_minb = value;
     else if (n == "direct_minb") rtb::g_tune.direct_minb = value;
     else if (n == "refill_idle") rtb::g_tune.refill_idle = std::max(1, std::min(value, 32));
@@ -389,6 +391,16 @@ static int make_scene(rtb_context* c, SceneDev& sc)
     sc.tlas_nodes = c->tlas.nodes; sc.tlas_index = (const int*)c->tlas.order; sc.inst = c->inst_d; sc.meshes = c->meshes_d;
     sc.materials = c->materials_d; sc.num_instances = (int)c->instances_h.size(); sc.num_materials = (int)c->materials_h.size();
     sc.tlas_extent = bounds_extent(c->tlas.bounds, sc.num_instances);
+    // top tree levels to stage in shared memory (rtb_tma.cuh): the TLAS prefix and the prefix of the BLAS most instances use
+    sc.top_blas = nullptr; sc.top_tlas_n = sc.top_blas_n = 0;
+    if (rtb::g_tune.smem_top > 0 && !c->instances_h.empty()) {
+        std::vector<int> uses(c->meshes.size(), 0);
+        for (const auto& in : c->instances_h) uses[in.mesh_index]++;
+        const int best = (int)(std::max_element(uses.begin(), uses.end()) - uses.begin());
+        const MeshRec& m = c->meshes[best];
+        if (m.bvh.nodes && m.bvh.num_nodes > 0) { sc.top_blas = m.bvh.nodes; sc.top_blas_n = std::min(m.bvh.num_nodes, rtb::g_tune.smem_top); }
+        if (sc.num_instances > 1) sc.top_tlas_n = std::min(c->tlas.num_nodes, 48);
+    }
     return RTB_OK;
 }
 

@@ -49,6 +49,9 @@ struct SceneDev {
     int num_instances;
     int num_materials;
     float tlas_extent;              // largest |coordinate| of any instance world box
+    // top tree levels staged into shared memory by the persistent kernels (rtb_tma.cuh); 0 counts = not staged
+    const float4* top_blas;         // node array of the BLAS whose first top_blas_n nodes are staged
+    int top_tlas_n, top_blas_n;
 };
 
 struct FrameParams {

@@ -8,6 +8,8 @@ namespace rtb {
 struct Tune {
     int trace_minb = 8;     // __launch_bounds__(128, N) variant of the queue tracer: resident blocks per SM the registers allow
     int direct_minb = 8;    // same for the direct kernel
+    int fused = 1;          // modes 2/3: 1 = one persistent path kernel (rtb_mega.cu), 0 = staged wavefront pipeline (rtb_wavefront.cu)
+    int smem_top = 0;       // BLAS nodes (top levels, BFS prefix) staged in shared memory by TMA bulk copy; 0 = off (measured slower: profiles/r01e_tune_c3_smem_top.log)
     int refill_idle = 28;   // queue tracer: refill a warp once this many lanes are idle
 };
 extern Tune g_tune;

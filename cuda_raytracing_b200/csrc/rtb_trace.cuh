@@ -10,6 +10,7 @@
 // (instance, original triangle index) instead of by the reference's traversal order.
 #pragma once
 #include "rtb_internal.cuh"
+#include "rtb_tma.cuh"
 
 namespace rtb {
 
@@ -45,12 +46,17 @@ XF void setup_slabs(InstRay& r)
 }
 
 // 4 slab tests against one wide node; keys[i] = (bits(tnear) & ~3) | i for hits, 0xffffffff for misses
+// GENERIC: the node may live in shared memory (staged top levels), so plain generic loads instead of ld.global.nc
+template <bool GENERIC>
+XF float4 node_ld(const float4* p) { return GENERIC ? *p : __ldg(p); }
+
+template <bool GENERIC>
 XF void test_node(const float4* __restrict__ node, const InstRay& r, float tmax, unsigned keys[4], int4& refs)
 {
-    const float4 nxv = __ldg(node + r.nx), fxv = __ldg(node + (r.nx ^ 1));
-    const float4 nyv = __ldg(node + r.ny), fyv = __ldg(node + (r.ny ^ 1));
-    const float4 nzv = __ldg(node + r.nz), fzv = __ldg(node + (r.nz ^ 1));
-    const float4 rf = __ldg(node + 6);
+    const float4 nxv = node_ld<GENERIC>(node + r.nx), fxv = node_ld<GENERIC>(node + (r.nx ^ 1));
+    const float4 nyv = node_ld<GENERIC>(node + r.ny), fyv = node_ld<GENERIC>(node + (r.ny ^ 1));
+    const float4 nzv = node_ld<GENERIC>(node + r.nz), fzv = node_ld<GENERIC>(node + (r.nz ^ 1));
+    const float4 rf = node_ld<GENERIC>(node + 6);
     refs = make_int4(__float_as_int(rf.x), __float_as_int(rf.y), __float_as_int(rf.z), __float_as_int(rf.w));
     const float ax[4] = { nxv.x, nxv.y, nxv.z, nxv.w }, bx[4] = { fxv.x, fxv.y, fxv.z, fxv.w };
     const float ay[4] = { nyv.x, nyv.y, nyv.z, nyv.w }, by[4] = { fyv.x, fyv.y, fyv.z, fyv.w };

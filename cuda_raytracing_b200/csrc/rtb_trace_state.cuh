@@ -30,6 +30,7 @@ struct RegSink {
     XF float min() const { return hit.min; }
     XF int inst() const { return hit.inst; }
     XF int prim() const { return hit.prim; }
+    XF bool any_hit() const { return false; }
     XF void accept(float distance, int slot, int prim, int inst, float u, float v, f3 loc)
     {
         hit.min = distance; hit.slot = slot; hit.prim = prim; hit.inst = inst; hit.u = u; hit.v = v; hit.loc = loc;
@@ -104,6 +105,14 @@ struct TraceState {
     template <bool ANY, bool COUNT, class Sink>
     XF void advance(const SceneDev& sc, uint2* __restrict__ stk, Sink& sink)
     {
+        TopLevels none; none.n_tlas = none.n_blas = 0; none.s_tlas = none.s_blas = none.g_blas = nullptr;
+        advance<ANY, COUNT, false>(sc, stk, sink, none);
+    }
+
+    // SMEM: nodes whose index is below the staged count of their array are read from shared memory (rtb_tma.cuh)
+    template <bool ANY, bool COUNT, bool SMEM, class Sink>
+    XF void advance(const SceneDev& sc, uint2* __restrict__ stk, Sink& sink, const TopLevels& T)
+    {
         if (++guard > (1u << 22)) { overflow = true; cur = EMPTY_REF; }   // a frame can never hang the device
         // Speculative traversal: the first triangle leaf a lane meets is postponed (`pend`) and the lane keeps walking
         // interior nodes, so it does useful work while the slower lanes of the warp are still descending; the loop
@@ -113,7 +122,12 @@ struct TraceState {
             unsigned k[4]; int4 refs;
             if (COUNT) n_nodes++;
             if (sp + 3 > STACK_CAP) { overflow = true; cur = EMPTY_REF; break; }
-            test_node(nodes + (size_t)cur * NODE_F4, r, tmax, k, refs);
+            const float4* np = nodes + (size_t)cur * NODE_F4;
+            if (SMEM) {
+                if (!in_blas) { if (cur < T.n_tlas) np = T.s_tlas + cur * NODE_F4; }
+                else if (cur < T.n_blas && nodes == T.g_blas) np = T.s_blas + cur * NODE_F4;
+            }
+            test_node<SMEM>(np, r, tmax, k, refs);
             RTB_CSWAP(k[0], k[1]); RTB_CSWAP(k[2], k[3]); RTB_CSWAP(k[0], k[2]); RTB_CSWAP(k[1], k[3]); RTB_CSWAP(k[1], k[2]);
             const int c0 = sel4(k[0] & 3u, refs), c1 = sel4(k[1] & 3u, refs), c2 = sel4(k[2] & 3u, refs), c3 = sel4(k[3] & 3u, refs);
             // far first, so the nearer children are popped first (misses sort last: key 0xffffffff)
@@ -180,7 +194,7 @@ struct TraceState {
                 found = true;
             }
         }
-        if (ANY && found) { cur = EMPTY_REF; return; }
+        if ((ANY || sink.any_hit()) && found) { cur = EMPTY_REF; return; }
         if (cur_leaf) cur = pop(stk);
         // events: leave the instance (sentinel popped), enter the instance of a TLAS leaf
         if (cur == LEAVE_REF) {                 // instance exhausted: back to world space

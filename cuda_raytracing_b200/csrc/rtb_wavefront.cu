@@ -13,8 +13,7 @@
 // and k_resolve converts the per-pixel radiance to the 8-bit BGR frame.
 // Queue records: ray 2 x float4 (origin|pixel, direction), hit 2 x float4 (min,u,v,inst | location,slot),
 // shadow 3 x float4 (origin|pixel, throughput|w, colour|cos).  Per-pixel throughput / radiance: float4 arrays.
-#include "rtb_render.cuh"
-#include "rtb_shade.cuh"
+#include "rtb_wave_common.cuh"
 #include <algorithm>
 
 struct rtb_context;
@@ -32,53 +31,12 @@ struct WaveState {
     int* counters = nullptr;        // 4 ints per (pass, bounce): ray count, ray head, shadow count, shadow head
     size_t cap_rays = 0, cap_pixels = 0;
     int n_counters = 0;
+    void* mega = nullptr;           // state of the fused persistent kernel (rtb_mega.cu)
 };
 
-__constant__ float c_sky[3] = { 1.0f, 0.8f, 0.6f };     // raycast.cu:210-213 (BGR)
-
-// Philox4x32-10, identical to oracle/rt_oracle.c
-XF void philox4x32(unsigned c[4], unsigned k0, unsigned k1)
-{
-#pragma unroll
-    for (int r = 0; r < 10; r++) {
-        unsigned long long p0 = (unsigned long long)0xD2511F53u * c[0], p1 = (unsigned long long)0xCD9E8D57u * c[2];
-        unsigned n0 = (unsigned)(p1 >> 32) ^ c[1] ^ k0, n1 = (unsigned)p1;
-        unsigned n2 = (unsigned)(p0 >> 32) ^ c[3] ^ k1, n3 = (unsigned)p0;
-        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-    }
-}
-XF float u01(unsigned x) { return xm((float)(x >> 8), 1.0f / 16777216.0f); }
-
-XF f3 reflect_dir(f3 d, f3 n)
-{
-    const float k = xm(2.0f, xdot(d, n));
-    return xnormalize(xsub(d, xscale(n, k)));
-}
-
-XF f3 cosine_dir(f3 n, float u1, float u2)
-{
-    const float r = __fsqrt_rn(u1), phi = xm(6.2831853f, u2);
-    const float lx = xm(r, cosf(phi)), ly = xm(r, sinf(phi)), lz = __fsqrt_rn(fmaxf(0.0f, xs(1.0f, u1)));
-    const float sign = copysignf(1.0f, n.z);
-    const float a = xd(-1.0f, xa(sign, n.z));
-    const float b = xm(xm(n.x, n.y), a);
-    const f3 t = mk3(xa(1.0f, xm(xm(xm(sign, n.x), n.x), a)), xm(sign, b), xm(-sign, n.x));
-    const f3 bt = mk3(b, xa(sign, xm(xm(n.y, n.y), a)), -n.y);
-    return xnormalize(xadd(xadd(xscale(t, lx), xscale(bt, ly)), xscale(n, lz)));
-}
-
-// index within this rank's pixel set -> pixel coordinates (8x4 warp tiles, BAND_ROWS-row bands)
-XF bool local_to_pixel(const FrameParams& P, int idx, int tiles_x, int& x, int& y)
-{
-    const int tile = idx >> 5, l = idx & 31;
-    const int tx = tile % tiles_x, ty = tile / tiles_x;
-    x = tx * 8 + (l & 7);
-    const int yl = ty * 4 + (l >> 3);
-    const int band = (yl / BAND_ROWS) * P.tile_count + P.tile_rank;
-    y = band * BAND_ROWS + (yl % BAND_ROWS);
-    return x < P.width && y < P.height;
-}
+cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
+                        const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st);
+void mega_release(void* state);
 
 // ------------------------------------------------------------------ stage 0: camera rays
 template <bool PATH>
@@ -112,6 +70,7 @@ struct QueueSink {
     XF float min() const { return hmin; }
     XF int inst() const { return hinst; }
     XF int prim() const { return hprim; }
+    XF bool any_hit() const { return false; }
     XF void accept(float distance, int slot, int prim, int inst, float u, float v, f3 loc)
     {
         hmin = distance; hinst = inst; hprim = prim;
@@ -337,6 +296,7 @@ cudaError_t launch_wavefront(rtb_context*, void** state, const SceneDev& sc, con
 {
     WaveState* w = (WaveState*)*state;
     if (!w) { w = new WaveState(); *state = w; }
+    if (g_tune.fused) return launch_mega(&w->mega, sc, P, img, pitch, aov, ctr, count, st);
     const bool path = P.mode == RTB_MODE_PATH;
     const int bands = (P.height + BAND_ROWS - 1) / BAND_ROWS;
     const int my_bands = (bands - P.tile_rank + P.tile_count - 1) / P.tile_count;
@@ -402,6 +362,7 @@ void wave_release(void* state)
     if (!state) return;
     WaveState* w = (WaveState*)state;
     wave_free(w);
+    mega_release(w->mega);
     delete w;
 }
 
