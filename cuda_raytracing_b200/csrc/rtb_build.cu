@@ -121,8 +121,9 @@ __global__ void k_morton(const float4* __restrict__ bmin, const float4* __restri
         unsigned ix = min(1023u, (unsigned)(nx * 1024.f)), iy = min(1023u, (unsigned)(ny * 1024.f)), iz = min(1023u, (unsigned)(nz * 1024.f));
         keys[i] = (K)((expand10(ix) << 2) | (expand10(iy) << 1) | expand10(iz));
     } else {
-        unsigned long long ix = min(2097151u, (unsigned)(nx * 2097152.f)), iy = min(2097151u, (unsigned)(ny * 2097152.f)),
-                           iz = min(2097151u, (unsigned)(nz * 2097152.f));
+        // 16 bits per axis = 48-bit keys: six 8-bit radix passes instead of eight, still 2^48 cells
+        unsigned long long ix = min(65535u, (unsigned)(nx * 65536.f)), iy = min(65535u, (unsigned)(ny * 65536.f)),
+                           iz = min(65535u, (unsigned)(nz * 65536.f));
         keys[i] = (K)((expand21(ix) << 2) | (expand21(iy) << 1) | expand21(iz));
     }
     vals[i] = (unsigned)i;
@@ -339,7 +340,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     keys[0] = ws.take<K>(n); keys[1] = ws.take<K>(n);
     vals[0] = ws.take<unsigned>(n); vals[1] = ws.take<unsigned>(n);
     const int nblocks = (n + RS_TILE - 1) / RS_TILE;
-    unsigned* hist = ws.take<unsigned>((size_t)256 * nblocks);
+    unsigned* hist = ws.take<unsigned>((size_t)256 * nblocks + 256);
     int* left = ws.take<int>(n); int* right = ws.take<int>(n);
     int* parent = ws.take<int>(2 * (size_t)n); int2* range = ws.take<int2>(n);
     int* visit = ws.take<int>(n);
@@ -404,7 +405,7 @@ cudaError_t build_bvh(const float4* bmin, const float4* bmax, int n, int max_lea
         k_trivial_root<<<1, 1, 0, st>>>(out.nodes, bmin, bmax, n);
         if (n == 1) k_iota<<<1, 32, 0, st>>>(out.order, 1);
     } else if (wide_keys) {
-        CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 64, out, ws, ctr, st));
+        CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 48, out, ws, ctr, st));
     } else {
         CK(build_tree<unsigned>(bmin, bmax, n, max_leaf, 32, out, ws, ctr, st));
     }

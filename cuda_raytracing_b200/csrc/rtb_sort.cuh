@@ -33,36 +33,53 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist(const K* __restrict__ keys
     hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of `total` unsigned values in place, one block of 1024 threads
-__global__ void __launch_bounds__(1024) rs_scan(unsigned* __restrict__ data, int total)
+// Exclusive scan of the digit-major histogram table, in two levels so that it runs on 256 CTAs instead of one:
+// rs_scan_rows: CTA d scans row d (the tile counts of digit d) in place and writes the row total;
+// the 256 row totals are prefix-summed by every scatter CTA itself (one warp-shuffle scan, rs_scatter).
+__global__ void __launch_bounds__(256) rs_scan_rows(unsigned* __restrict__ data, int nblocks, unsigned* __restrict__ totals)
 {
-    __shared__ unsigned part[1024];
+    __shared__ unsigned part[256];
+    unsigned* row = data + (size_t)blockIdx.x * nblocks;
     const int t = threadIdx.x;
-    const int per = (total + 1023) / 1024;
-    const int b = t * per, e = min(b + per, total);
+    const int per = (nblocks + 255) / 256;
+    const int b = min(t * per, nblocks), e = min(b + per, nblocks);
     unsigned s = 0;
-    for (int i = b; i < e; i++) s += data[i];
+    for (int i = b; i < e; i++) s += row[i];
     part[t] = s;
     __syncthreads();
-    for (int off = 1; off < 1024; off <<= 1) {         // Hillis-Steele inclusive scan
+    for (int off = 1; off < 256; off <<= 1) {          // Hillis-Steele inclusive scan
         unsigned v = t >= off ? part[t - off] : 0u;
         __syncthreads();
         part[t] += v;
         __syncthreads();
     }
     unsigned run = part[t] - s;
-    for (int i = b; i < e; i++) { unsigned v = data[i]; data[i] = run; run += v; }
+    for (int i = b; i < e; i++) { unsigned v = row[i]; row[i] = run; run += v; }
+    if (t == 255) totals[blockIdx.x] = part[255];
 }
 
 template <typename K>
 __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const K* __restrict__ keys_in, const unsigned* __restrict__ vals_in,
                                                          K* __restrict__ keys_out, unsigned* __restrict__ vals_out, int n,
-                                                         int shift, int nblocks, const unsigned* __restrict__ offs)
+                                                         int shift, int nblocks, const unsigned* __restrict__ offs,
+                                                         const unsigned* __restrict__ totals)
 {
     __shared__ unsigned cnt[RS_WARPS][256];
+    __shared__ unsigned dbase[256];                 // exclusive prefix of the 256 digit totals
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&cnt[0][0])[i] = 0;
     __syncthreads();
+    {   // thread d: exclusive prefix of totals[0..d): warp scan + warp sums (RS_THREADS == 256 digits)
+        const unsigned v = totals[threadIdx.x];
+        unsigned inc = v;
+        for (int o = 1; o < 32; o <<= 1) { unsigned u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+        if (lane == 31) dbase[w] = inc;             // reuse dbase[0..7] as warp sums for a moment
+        __syncthreads();
+        unsigned wsum = 0;
+        for (int ww = 0; ww < w; ww++) wsum += dbase[ww];
+        __syncthreads();
+        dbase[threadIdx.x] = wsum + inc - v;
+    }
     const int wbase = blockIdx.x * RS_TILE + w * (32 * RS_KPT);
     K key[RS_KPT];
     unsigned short off[RS_KPT];
@@ -87,7 +104,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const K* __restrict__ k
     __syncthreads();
     {   // digit column prefix across warps, seeded with this tile's global offset
         const int d = threadIdx.x;
-        unsigned run = offs[(size_t)d * nblocks + blockIdx.x];
+        unsigned run = offs[(size_t)d * nblocks + blockIdx.x] + dbase[d];
 #pragma unroll
         for (int ww = 0; ww < RS_WARPS; ww++) { unsigned c = cnt[ww][d]; cnt[ww][d] = run; run += c; }
     }
@@ -104,7 +121,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const K* __restrict__ k
     }
 }
 
-// Sorts `bits` low bits; result ends in (keys[0], vals[0]) or (keys[1], vals[1]); returns which.
+// `hist` holds 256 * nblocks + 256 counters.  Sorts `bits` low bits; result ends in (keys[0], vals[0]) or (keys[1], vals[1]); returns which.
 template <typename K>
 inline int radix_sort_pairs(K* keys[2], unsigned* vals[2], int n, int bits, unsigned* hist, cudaStream_t st)
 {
@@ -112,8 +129,9 @@ inline int radix_sort_pairs(K* keys[2], unsigned* vals[2], int n, int bits, unsi
     int cur = 0;
     for (int shift = 0; shift < bits; shift += 8) {
         rs_hist<K><<<nblocks, RS_THREADS, 0, st>>>(keys[cur], n, shift, nblocks, hist);
-        rs_scan<<<1, 1024, 0, st>>>(hist, 256 * nblocks);
-        rs_scatter<K><<<nblocks, RS_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, nblocks, hist);
+        rs_scan_rows<<<256, 256, 0, st>>>(hist, nblocks, hist + (size_t)256 * nblocks);
+        rs_scatter<K><<<nblocks, RS_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, nblocks, hist,
+                                                      hist + (size_t)256 * nblocks);
         cur ^= 1;
     }
     return cur;
