@@ -53,7 +53,7 @@ struct rtb_context {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
     int last_launches = 0;
-    int opt_counters = 0, opt_leaf = 4, opt_key_bits = 0;
+    int opt_counters = 0, opt_leaf = 8, opt_key_bits = 0;
     void* wf = nullptr;            // wavefront state (rtb_wavefront.cu)
 };
 
@@ -129,6 +129,7 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
     else if (n == "key_bits") c->opt_key_bits = value;
     else if (n == "fused") rtb::g_tune.fused = value;
+    else if (n == "spec_thr") rtb::g_tune.spec_thr = std::max(0, std::min(value, 31));
     else if (n == "smem_top") rtb::g_tune.smem_top = std::max(0, std::min(value, 341));
     else if (n == "trace_minb") rtb::g_tune.trace_minb = value;
     else if (n == "direct_minb") rtb::g_tune.direct_minb = value;
@@ -393,6 +394,7 @@ static int make_scene(rtb_context* c, SceneDev& sc)
     sc.tlas_extent = bounds_extent(c->tlas.bounds, sc.num_instances);
     // top tree levels to stage in shared memory (rtb_tma.cuh): the TLAS prefix and the prefix of the BLAS most instances use
     sc.top_blas = nullptr; sc.top_tlas_n = sc.top_blas_n = 0;
+    sc.spec_thr = rtb::g_tune.spec_thr;
     if (rtb::g_tune.smem_top > 0 && !c->instances_h.empty()) {
         std::vector<int> uses(c->meshes.size(), 0);
         for (const auto& in : c->instances_h) uses[in.mesh_index]++;

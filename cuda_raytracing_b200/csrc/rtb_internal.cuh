@@ -52,6 +52,7 @@ struct SceneDev {
     // top tree levels staged into shared memory by the persistent kernels (rtb_tma.cuh); 0 counts = not staged
     const float4* top_blas;         // node array of the BLAS whose first top_blas_n nodes are staged
     int top_tlas_n, top_blas_n;
+    int spec_thr;                   // speculative traversal: leave the interior loop once at most this many lanes hold no postponed leaf
 };
 
 struct FrameParams {

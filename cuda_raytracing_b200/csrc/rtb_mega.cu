@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, SceneDev sc
     TopLevels T;
     T.n_tlas = T.n_blas = 0; T.s_tlas = T.s_blas = T.g_blas = nullptr;
     if (SMEM) stage_top_levels(sc, s_top, T);
-    uint2 stk[STACK_CAP];
+    RTB_DECL_STACK(stk);
     TraceState S;
     MegaSink sink;
     sink.h0 = B.hit0; sink.h1 = B.hit1;

@@ -31,8 +31,9 @@ __global__ void __launch_bounds__(128, MINB) k_render_direct(SceneDev sc, FrameP
     const f3 origin = mk3(P.ox, P.oy, P.oz);
     f3 dir = mk3(0.f, 0.f, 1.f);
     if (valid) dir = generate_direction(P, (float)x, (float)y);
+    RTB_DECL_STACK(stk);
     Hit h;
-    trace<false, COUNT>(sc, valid, origin, dir, h, ctr);
+    trace<false, COUNT>(sc, stk, valid, origin, dir, h, ctr);
     const bool is_hit = valid && h.min != FLT_MAX;
     InstXf xf;
     f3 c = mk3(0.f, 0.f, 0.f), nrm = mk3(0.f, 0.f, 1.f);
@@ -42,7 +43,7 @@ __global__ void __launch_bounds__(128, MINB) k_render_direct(SceneDev sc, FrameP
         if (LIT) nrm = world_normal(sc, h, xf);
     }
     float illum = 1.0f;                                                            // raycast.cu:282
-    if (LIT) illum = lit_illumination<COUNT>(sc, P, is_hit, h, nrm, ctr, rays);
+    if (LIT) illum = lit_illumination<COUNT>(sc, stk, P, is_hit, h, nrm, ctr, rays);
     if (valid) {
         rays++;
         const size_t pi = (size_t)y * P.width + x;

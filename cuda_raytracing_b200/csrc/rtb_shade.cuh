@@ -66,7 +66,7 @@ XF float clamp01(float v) { return fminf(1.0f, fmaxf(0.0f, v)); }
 // Returns the clamped illumination (289-290); counts the any-hit ray if one was cast.  Warp-collective: every
 // lane calls it, lanes without a hit pass lit=false.
 template <bool COUNT>
-XF float lit_illumination(const SceneDev& sc, const FrameParams& P, bool lit, const Hit& h, f3 nrm, Counters* ctr, unsigned& rays)
+XF float lit_illumination(const SceneDev& sc, Stack& stk, const FrameParams& P, bool lit, const Hit& h, f3 nrm, Counters* ctr, unsigned& rays)
 {
     const f3 L = mk3(P.light_dir.x, P.light_dir.y, P.light_dir.z);
     const float cos_illum = lit ? xdot(nrm, L) : 0.0f;
@@ -74,7 +74,7 @@ XF float lit_illumination(const SceneDev& sc, const FrameParams& P, bool lit, co
     const bool cast = lit && cos_illum > 0.0f;
     const f3 so = xadd(h.loc, xscale(L, 1e-4f));                       // raycast.cu:259
     Hit sh;
-    trace<true, COUNT>(sc, cast, so, L, sh, ctr);
+    trace<true, COUNT>(sc, stk, cast, so, L, sh, ctr);
     if (cast) {
         rays++;
         if (sh.min == FLT_MAX) illum = cos_illum;

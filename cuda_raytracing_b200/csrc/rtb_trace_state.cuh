@@ -22,6 +22,28 @@ namespace rtb {
 
 constexpr int LEAVE_REF = (int)0x80000001;     // sentinel stack entry: instance exhausted, restore the world-space ray
 
+// Traversal stack of (tnear bits, ref) entries.  Default: a per-thread local-memory array.  With -DRTB_SMEM_STACK the
+// first SMEM_STACK_DEPTH entries live in shared memory (column of this thread, stride = 128 threads, conflict-free for
+// lanes at the same depth) and only deeper entries spill to local memory.
+constexpr int SMEM_STACK_DEPTH = 12;
+struct Stack {
+#ifdef RTB_SMEM_STACK
+    uint2* sm;
+    uint2 loc[STACK_CAP - SMEM_STACK_DEPTH];
+    XF void put(int i, uint2 v) { if (i < SMEM_STACK_DEPTH) sm[i * 128] = v; else loc[i - SMEM_STACK_DEPTH] = v; }
+    XF uint2 get(int i) const { return i < SMEM_STACK_DEPTH ? sm[i * 128] : loc[i - SMEM_STACK_DEPTH]; }
+#else
+    uint2 loc[STACK_CAP];
+    XF void put(int i, uint2 v) { loc[i] = v; }
+    XF uint2 get(int i) const { return loc[i]; }
+#endif
+};
+#ifdef RTB_SMEM_STACK
+#define RTB_DECL_STACK(name) __shared__ uint2 name##_sm[SMEM_STACK_DEPTH * 128]; Stack name; name.sm = name##_sm + threadIdx.x
+#else
+#define RTB_DECL_STACK(name) Stack name
+#endif
+
 // Hit record kept in registers (direct kernel).  The queue tracer uses a sink that writes accepted candidates
 // straight to the hit queue in HBM and keeps only what the accept rule compares (rtb_wavefront.cu).
 struct RegSink {
@@ -51,7 +73,7 @@ struct TraceState {
     XF void clear() { cur = EMPTY_REF; sp = 0; n_nodes = n_tris = guard = 0; overflow = false; in_blas = false; cur_inst = -1; }
 
     // raycast.cu:33-45: r_dir = apply_euler(rotation, dir) * inv_scale ; r_org = apply_lre(pose, org) * inv_scale
-    XF void enter_instance(const SceneDev& sc, int inst, uint2* __restrict__ stk, bool sentinel)
+    XF void enter_instance(const SceneDev& sc, int inst, Stack& stk, bool sentinel)
     {
         const float4* p = sc.inst + (size_t)inst * INST_F4;
         const float4 q_pose = __ldg(p + 0), b = __ldg(p + 1), c = __ldg(p + 2);
@@ -63,11 +85,11 @@ struct TraceState {
         const MeshDev* m = sc.meshes + __float_as_int(b.w);
         nodes = m->nodes; tris = m->tris;
         in_blas = true;
-        if (sentinel) stk[sp++] = make_uint2(0xbf800000u /* -1.0f: never culled */, (unsigned)LEAVE_REF);
+        if (sentinel) stk.put(sp++, make_uint2(0xbf800000u /* -1.0f: never culled */, (unsigned)LEAVE_REF));
         cur = 0;                                // BLAS root
     }
 
-    XF void begin(const SceneDev& sc, f3 o, f3 d, uint2* __restrict__ stk)
+    XF void begin(const SceneDev& sc, f3 o, f3 d, Stack& stk)
     {
         org = o; dir = d;
         sp = 0; in_blas = false; cur_inst = -1;
@@ -85,10 +107,10 @@ struct TraceState {
         }
     }
 
-    XF int pop(const uint2* __restrict__ stk)
+    XF int pop(Stack& stk)
     {
         while (sp > 0) {
-            const uint2 e = stk[--sp];
+            const uint2 e = stk.get(--sp);
             if (__uint_as_float(e.x) < tmax) return (int)e.y;
         }
         return EMPTY_REF;
@@ -103,7 +125,7 @@ struct TraceState {
     static XF bool is_leaf_ref(int ref) { return (unsigned)ref > (unsigned)LEAVE_REF; }   // negative, not EMPTY / LEAVE
 
     template <bool ANY, bool COUNT, class Sink>
-    XF void advance(const SceneDev& sc, uint2* __restrict__ stk, Sink& sink)
+    XF void advance(const SceneDev& sc, Stack& stk, Sink& sink)
     {
         TopLevels none; none.n_tlas = none.n_blas = 0; none.s_tlas = none.s_blas = none.g_blas = nullptr;
         advance<ANY, COUNT, false>(sc, stk, sink, none);
@@ -111,7 +133,7 @@ struct TraceState {
 
     // SMEM: nodes whose index is below the staged count of their array are read from shared memory (rtb_tma.cuh)
     template <bool ANY, bool COUNT, bool SMEM, class Sink>
-    XF void advance(const SceneDev& sc, uint2* __restrict__ stk, Sink& sink, const TopLevels& T)
+    XF void advance(const SceneDev& sc, Stack& stk, Sink& sink, const TopLevels& T)
     {
         if (++guard > (1u << 22)) { overflow = true; cur = EMPTY_REF; }   // a frame can never hang the device
         // Speculative traversal: the first triangle leaf a lane meets is postponed (`pend`) and the lane keeps walking
@@ -131,14 +153,14 @@ struct TraceState {
             RTB_CSWAP(k[0], k[1]); RTB_CSWAP(k[2], k[3]); RTB_CSWAP(k[0], k[2]); RTB_CSWAP(k[1], k[3]); RTB_CSWAP(k[1], k[2]);
             const int c0 = sel4(k[0] & 3u, refs), c1 = sel4(k[1] & 3u, refs), c2 = sel4(k[2] & 3u, refs), c3 = sel4(k[3] & 3u, refs);
             // far first, so the nearer children are popped first (misses sort last: key 0xffffffff)
-            if (k[3] != 0xffffffffu) stk[sp++] = make_uint2(k[3] & ~3u, (unsigned)c3);
-            if (k[2] != 0xffffffffu) stk[sp++] = make_uint2(k[2] & ~3u, (unsigned)c2);
-            if (k[1] != 0xffffffffu) stk[sp++] = make_uint2(k[1] & ~3u, (unsigned)c1);
+            if (k[3] != 0xffffffffu) stk.put(sp++, make_uint2(k[3] & ~3u, (unsigned)c3));
+            if (k[2] != 0xffffffffu) stk.put(sp++, make_uint2(k[2] & ~3u, (unsigned)c2));
+            if (k[1] != 0xffffffffu) stk.put(sp++, make_uint2(k[1] & ~3u, (unsigned)c1));
             int nxt = c0;
             if (k[0] == 0xffffffffu) nxt = pop(stk);
             if (in_blas && pend == EMPTY_REF && is_leaf_ref(nxt)) { pend = nxt; nxt = pop(stk); }
             cur = nxt;
-            if (!__any_sync(__activemask(), pend == EMPTY_REF)) break;
+            if (__popc(__ballot_sync(__activemask(), pend == EMPTY_REF)) <= sc.spec_thr) break;
         }
         // Reconvergence point: every lane of the warp calls advance() (both drivers guarantee it), and without this
         // barrier lanes leave the interior loop in small groups and run the leaf code 2 lanes wide (ncu, profiles/r01b).
@@ -225,9 +247,8 @@ struct TraceState {
 // lighting_pass early-out of raycast.cu:128-132) for one ray.
 // Must be called by all 32 lanes of the warp (advance() holds a warp barrier); lanes without a ray pass active=false.
 template <bool ANY, bool COUNT>
-__device__ __forceinline__ void trace(const SceneDev& sc, bool active, f3 org, f3 dir, Hit& hit, Counters* ctr)
+__device__ __forceinline__ void trace(const SceneDev& sc, Stack& stk, bool active, f3 org, f3 dir, Hit& hit, Counters* ctr)
 {
-    uint2 stk[STACK_CAP];
     TraceState S;
     RegSink sink;
     sink.reset();

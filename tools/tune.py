@@ -10,6 +10,8 @@ import bench
 from cuda_raytracing_b200 import api
 
 def main():
+    if os.environ.get("RTB_VARIANT"):                       # A/B a differently compiled library (tools/variants/*.so)
+        api.LIB_PATH = os.path.join(ROOT, "tools", "variants", os.environ["RTB_VARIANT"])
     name = sys.argv[1]
     knobs = [(a.split("=")[0], [int(v) for v in a.split("=")[1].split(",")]) for a in sys.argv[2:]]
     cfg = bench.CONFIGS[name]
@@ -17,6 +19,8 @@ def main():
     K, D = bench.config_K(cfg)
     tris = bench.build_tris(cfg)
     scene = api.Scene(0)
+    for kv in os.environ.get("PRE", "").split():           # options that must be set before the upload, e.g. PRE="leaf_size=8"
+        scene.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     for m in bench.scene_materials(cfg):
         scene.add_material(api.Material(albedo=m["albedo"], metallic=m["metallic"]))
     scene.add_mesh(api.MeshPrimitive(tris))
