@@ -51,7 +51,7 @@ def main():
             ref = h
         rays = scene.frame_stats()["rays"]
         print(json.dumps(dict(config=name, knobs=dict(zip([k for k, _ in knobs], combo)), ms=round(float(np.mean(ms)), 3), ms_min=round(min(ms), 3),
-                              mrays=round(rays / np.mean(ms) / 1e3, 1), same_image=(h == ref))), flush=True)
+                              mrays=round(rays / np.mean(ms) / 1e3, 1), same_image=(h == ref), hash=h)), flush=True)
     scene.close()
 
 if __name__ == "__main__":
