@@ -322,11 +322,17 @@ def main():
         torch.cuda.synchronize()
         kms = e0.elapsed_time(e1)
         ach = alg_bytes / (kms * 1e-3) / 1e9
-        roof = dict(bound="hbm", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None, peak_kind=peak_kind,
-                    kernel="k_wave/k_render_direct (trace+shade)", kernel_ms=kms, nodes_per_ray=st["nodes"] / max(1, st["rays"]),
+        kname = "k_mega (fused persistent path kernel)" if cfg["mode"] >= 2 else "k_render_direct"
+        traffic = None                                   # dram bytes per launch of that kernel from the committed ncu --set full capture
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(args.config)
+        roof = dict(bound="hbm", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=traffic, peak_kind=peak_kind,
+                    kernel=kname, kernel_ms=kms, nodes_per_ray=st["nodes"] / max(1, st["rays"]),
                     tris_per_ray=st["tris"] / max(1, st["rays"]), rays=st["rays"], alg_bytes=alg_bytes,
-                    note="algorithmic bytes = 128 B/node visit + 64 B/triangle test + 3 B/pixel + 64 B/queue hop; the BLAS "
-                         "(~110 MB) is L2-resident, so achieved can exceed the HBM copy peak")
+                    note="algorithmic bytes = 128 B/node visit + 64 B/triangle test + 3 B/pixel (+ 64 B/queue hop, staged pipeline only); "
+                         "node and triangle fetches are mostly L1/L2 hits (BLAS ~100 MB), so the kernel is issue/latency bound, "
+                         "not HBM bound: see DESIGN.md 4 and profiles/")
         cam.tile_rank, cam.tile_count = rank, world
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
