@@ -75,38 +75,61 @@ def scene_instances(cfg):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock, max clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe), through NVML
+    every ~2 ms so that even a sub-millisecond-per-step config is covered; nvidia-smi -lms is the fallback."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.stop_flag = index, [], None, False
+        self.sm, self.mx, self.reasons, self.how = [], [], set(), "nvml"
 
     def run(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].isdigit() else self.index
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            while not self.stop_flag:
+                self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                self.mx.append(mx)
+                try:
+                    bits = int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    bits = int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                for name, bit in self.REASONS:
+                    if bits & bit:
+                        self.reasons.add(name)
+                time.sleep(0.002)
+            return
+        except Exception:
+            self.how = "nvidia-smi"
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                           "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
-                self.rows.append([c.strip() for c in line.split(",")])
+                r = [c.strip() for c in line.split(",")]
+                if len(r) >= 9 and r[1].replace(".", "").isdigit():
+                    self.sm.append(float(r[1]))
+                    self.mx.append(float(r[2]))
+                    for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                        if v.lower().startswith("active"):
+                            self.reasons.add(name)
         except Exception:
             pass
 
     def stop(self):
+        self.stop_flag = True
         if self.proc:
             self.proc.terminate()
         self.join(timeout=2)
-        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
-        reasons = set()
-        for r in self.rows:
-            if len(r) >= 9:
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
-                    reasons=sorted(reasons), samples=len(sm))
+        return dict(sm_mhz=float(np.median(self.sm)) if self.sm else None, sm_max_mhz=max(self.mx) if self.mx else None,
+                    reasons=sorted(self.reasons), samples=len(self.sm), how=self.how)
 
 
 def load_peaks():
@@ -176,11 +199,15 @@ def run_reference(args, cfg, rank):
                 data="synthetic", config=dict(workload=cfg["desc"], config=args.config),
                 cpu_baseline=dict(value=val, unit="Mrays/s", cores=cores, kind=kind, sample=sample),
                 e2e=dict(value=val, unit="Mrays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------------------------------- our arm
 def main():
+    # stdout carries exactly ONE line, the JSON result: libraries that print banners on fd 1 (NCCL's version line) go to stderr
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(out_fd, "w")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -378,7 +405,7 @@ def main():
                     roofline=roof, cpu_baseline=cpu)
         if ref_cuda is not None:
             line["ref_cuda"] = ref_cuda
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     scene.close()

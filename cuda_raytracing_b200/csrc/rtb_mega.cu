@@ -34,7 +34,12 @@ struct MegaBufs {
 struct MegaState {
     MegaBufs b;
     int* head = nullptr;
+    unsigned* cost = nullptr;       // per coarse block, accumulated by the frame being rendered
+    int* order = nullptr;           // claim order of the blocks for the frame being rendered
     size_t cap = 0;
+    int nb_cap = 0;
+    // the cost map is only reused when the next frame has the same pixel set
+    int hist_w = 0, hist_h = 0, hist_rank = -1, hist_count = 0, hist_mode = -1;
 };
 
 // Accepted candidates go straight to the pixel's hit record; shadow rays (any-hit) record nothing.
@@ -67,9 +72,57 @@ XF f3 camera_ray(const FrameParams& P, int x, int y, int sample, bool path)
     return generate_direction(P, px, py);
 }
 
+// Claim order.  The rank-local pixel set is cut into coarse blocks of 8 x 8 warp tiles (64 x 32 pixels, 2048 slots);
+// a claimed slot index is (position of the block in `order`) * 2048 + (tile in block) * 32 + (pixel in tile).  `order`
+// lists the blocks by DESCENDING cost of the previous frame (longest-processing-time-first: the expensive pixels start
+// early, the cheap ones fill the end of the frame, so the tail of the one persistent launch is short); the cost of a
+// block is the number of traversal rounds its pixels took, accumulated by this kernel for the next frame.
+struct MegaGeo {
+    int tiles_x, tile_rows, nbx, nb, n_slots;
+    const int* order;               // nb entries or nullptr (identity)
+    unsigned* cost;                 // nb entries, accumulated this frame
+};
+constexpr int BLK_SLOTS = 2048;
+
+XF bool slot_to_pixel(const FrameParams& P, const MegaGeo& G, int idx, int& x, int& y, int& blk)
+{
+    const int k = idx >> 11, o = idx & (BLK_SLOTS - 1);
+    blk = G.order ? __ldg(G.order + k) : k;
+    const int bx = blk % G.nbx, by = blk / G.nbx;
+    const int t = o >> 5, l = o & 31;
+    const int tx = bx * 8 + (t & 7), ty = by * 8 + (t >> 3);
+    x = tx * 8 + (l & 7);
+    const int yl = ty * 4 + (l >> 3);
+    const int band = (yl / BAND_ROWS) * P.tile_count + P.tile_rank;
+    y = band * BAND_ROWS + (yl % BAND_ROWS);
+    return tx < G.tiles_x && ty < G.tile_rows && x < P.width && y < P.height;
+}
+
+// order[] = blocks sorted by descending log-bucketed cost (counting sort, one CTA), cost[] cleared for the new frame
+__global__ void __launch_bounds__(1024) k_order(unsigned* __restrict__ cost, int nb, int* __restrict__ order)
+{
+    __shared__ unsigned hist[256];
+    __shared__ unsigned offs[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+        const int key = 255 - min(255, (int)(log2f((float)cost[b] + 1.0f) * 8.0f));
+        atomicAdd(&hist[key], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { unsigned run = 0; for (int i = 0; i < 256; i++) { offs[i] = run; run += hist[i]; } }
+    __syncthreads();
+    for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+        const int key = 255 - min(255, (int)(log2f((float)cost[b] + 1.0f) * 8.0f));
+        order[atomicAdd(&offs[key], 1u)] = b;
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < nb; b += blockDim.x) cost[b] = 0u;
+}
+
 // meta word of the ray a lane is tracing: bit 0 = shadow ray, bits 1-7 = bounce, bits 8-31 = sample
 template <bool PATH, bool COUNT, int MINB, bool SMEM>
-__global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, SceneDev sc, FrameParams P, int n_local, int tiles_x,
+__global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_idle, SceneDev sc, FrameParams P, MegaGeo G,
                                                     int* __restrict__ head, MegaBufs B, unsigned char* __restrict__ img, size_t pitch,
                                                     int32_t* __restrict__ aov_prim, int32_t* __restrict__ aov_inst,
                                                     float* __restrict__ aov_t, Counters* ctr)
@@ -90,13 +143,13 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, SceneDev sc
     int idx = -1;                               // rank-local pixel slot this lane owns, -1 = none
     unsigned meta = 0;
     bool more = true;                           // warp-uniform: unclaimed pixels may remain
-    unsigned rays = 0;
+    unsigned rays = 0, steps = 0;                // steps: traversal rounds spent on the current pixel (cost map)
     for (;;) {
         const bool idle = S.cur == EMPTY_REF;
         // ---------------- retire the finished ray of every idle lane: shade, continue the chain or end the pixel
         if (idle && idx >= 0) {
-            int x, y;
-            local_to_pixel(P, idx, tiles_x, x, y);
+            int x, y, blk;
+            slot_to_pixel(P, G, idx, x, y, blk);
             const int pix = y * P.width + x;
             const int bounce = (int)((meta >> 1) & 127u), sample = (int)(meta >> 8);
             bool next = false, ended = false;
@@ -194,6 +247,7 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, SceneDev sc
                 p[0] = to_u8(xm(clamp01(xm(acc.x, scale)), 255.0f));
                 p[1] = to_u8(xm(clamp01(xm(acc.y, scale)), 255.0f));
                 p[2] = to_u8(xm(clamp01(xm(acc.z, scale)), 255.0f));
+                if ((idx & 7) == 0) atomicAdd(G.cost + blk, steps);       // 1 pixel in 8 reports: the map is a heuristic, the atomics are not free
                 idx = -1;
             }
         }
@@ -206,15 +260,15 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, SceneDev sc
             base = __shfl_sync(0xffffffffu, base, leader);
             if (idx < 0) {
                 const int i = base + __popc(fm & lt);
-                int x, y;
-                if (i < n_local && local_to_pixel(P, i, tiles_x, x, y)) {
-                    idx = i; meta = 0;
+                int x, y, blk;
+                if (i < G.n_slots && slot_to_pixel(P, G, i, x, y, blk)) {
+                    idx = i; meta = 0; steps = 0;
                     sink.reset(idx, false);
                     S.begin(sc, mk3(P.ox, P.oy, P.oz), camera_ray(P, x, y, 0, PATH), stk);
                     rays++;
                 }
             }
-            if (base + n >= n_local) more = false;
+            if (base + n >= G.n_slots) more = false;
         }
         const unsigned am = __ballot_sync(0xffffffffu, S.cur != EMPTY_REF);
         if (am == 0) {
@@ -223,9 +277,12 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, SceneDev sc
         }
         // trace until `refill_idle` of the lanes that can still get work are idle; lanes without a pixel are dead once
         // the counter is exhausted
+        // Tail of the frame (no unclaimed pixels left): retire as soon as `tail_idle` live lanes finish, so that the chains
+        // of a warp advance independently instead of in lock-step generations (each as long as its slowest ray).
         const int dead = more ? 0 : __popc(__ballot_sync(0xffffffffu, idx < 0));
-        const int keep = max(0, 32 - dead - refill_idle);
+        const int keep = more ? 32 - refill_idle : max(0, 32 - dead - tail_idle);
         do {
+            steps += S.cur != EMPTY_REF;
             S.template advance<false, COUNT, SMEM>(sc, stk, sink, T);
         } while (__popc(__ballot_sync(0xffffffffu, S.cur != EMPTY_REF)) > keep);
     }
@@ -241,7 +298,9 @@ static void mega_free(MegaState* m)
     float4** bufs[] = { &m->b.acc, &m->b.thr, &m->b.hit0, &m->b.hit1, &m->b.sp0, &m->b.sp1, &m->b.cont_o, &m->b.cont_d };
     for (auto p : bufs) { if (*p) cudaFree(*p); *p = nullptr; }
     if (m->head) cudaFree(m->head);
-    m->head = nullptr; m->cap = 0;
+    if (m->cost) cudaFree(m->cost);
+    if (m->order) cudaFree(m->order);
+    m->head = nullptr; m->cost = nullptr; m->order = nullptr; m->cap = 0; m->nb_cap = 0; m->hist_rank = -1;
 }
 
 void mega_release(void* state)
@@ -253,6 +312,7 @@ void mega_release(void* state)
 }
 
 extern int g_wave_launches;
+static int g_wave_launches_pre = 0;
 
 cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
                         const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st)
@@ -263,21 +323,34 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
     const int bands = (P.height + BAND_ROWS - 1) / BAND_ROWS;
     const int my_bands = (bands - P.tile_rank + P.tile_count - 1) / P.tile_count;
     if (my_bands <= 0) return cudaSuccess;
-    const int tiles_x = (P.width + 7) / 8;
-    const int n_local = tiles_x * 8 * my_bands * BAND_ROWS;           // padded pixel slots of this rank
-    if (P.max_depth > 126 || P.spp >= (1 << 24)) return cudaErrorInvalidValue;
-    if (m->cap < (size_t)n_local) {
+    MegaGeo G;
+    G.tiles_x = (P.width + 7) / 8;
+    G.tile_rows = my_bands * (BAND_ROWS / 4);
+    G.nbx = (G.tiles_x + 7) / 8;
+    G.nb = G.nbx * ((G.tile_rows + 7) / 8);
+    G.n_slots = G.nb * BLK_SLOTS;
+    if (P.max_depth > 126 || P.spp >= (1 << 24) || G.nb > (1 << 20)) return cudaErrorInvalidValue;
+    if (m->cap < (size_t)G.n_slots || m->nb_cap < G.nb) {
         mega_free(m);
         float4** bufs[] = { &m->b.acc, &m->b.thr, &m->b.hit0, &m->b.hit1, &m->b.sp0, &m->b.sp1, &m->b.cont_o, &m->b.cont_d };
-        for (auto p : bufs) MCK(cudaMalloc((void**)p, sizeof(float4) * (size_t)n_local));
+        for (auto p : bufs) MCK(cudaMalloc((void**)p, sizeof(float4) * (size_t)G.n_slots));
         MCK(cudaMalloc((void**)&m->head, sizeof(int)));
-        m->cap = (size_t)n_local;
+        MCK(cudaMalloc((void**)&m->cost, sizeof(unsigned) * (size_t)G.nb));
+        MCK(cudaMalloc((void**)&m->order, sizeof(int) * (size_t)G.nb));
+        m->cap = (size_t)G.n_slots; m->nb_cap = G.nb;
     }
+    const bool have_hist = g_tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
+                           m->hist_count == P.tile_count && m->hist_mode == P.mode;
+    if (have_hist) { k_order<<<1, 1024, 0, st>>>(m->cost, G.nb, m->order); g_wave_launches_pre = 1; }
+    else { MCK(cudaMemsetAsync(m->cost, 0, sizeof(unsigned) * (size_t)G.nb, st)); g_wave_launches_pre = 0; }
+    G.order = have_hist ? m->order : nullptr;
+    G.cost = m->cost;
+    m->hist_w = P.width; m->hist_h = P.height; m->hist_rank = P.tile_rank; m->hist_count = P.tile_count; m->hist_mode = P.mode;
     MCK(cudaMemsetAsync(m->head, 0, sizeof(int), st));
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    g_wave_launches = 0;
+    g_wave_launches = g_wave_launches_pre;
     if (path && (aov.prim || aov.inst || aov.t)) {
         FrameParams Q = P; Q.mode = RTB_MODE_REFERENCE;                 // first-hit AOVs from the un-jittered centre ray
         MCK(launch_render(sc, Q, img, pitch, aov, ctr, count, st));
@@ -285,12 +358,12 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
     }
     const int mb = g_tune.trace_minb <= 4 ? 4 : (g_tune.trace_minb == 5 ? 5 : (g_tune.trace_minb == 6 ? 6 : 8));
     const int ri = g_tune.refill_idle;
-    const int grid = std::min(sms * (count ? 4 : mb), (n_local + 127) / 128);
+    const int grid = std::min(sms * (count ? 4 : mb), (G.n_slots + 127) / 128);
     const bool smem = sc.top_tlas_n + sc.top_blas_n > 0;
     const size_t shb = smem ? (size_t)(sc.top_tlas_n + sc.top_blas_n) * 128 + 16 : 0;
-#define RTB_MEGA(PATH, COUNT, MINB) do { if (smem) k_mega<PATH, COUNT, MINB, true><<<grid, 128, shb, st>>>(ri, sc, P, n_local, tiles_x, m->head, m->b, img, pitch, \
+#define RTB_MEGA(PATH, COUNT, MINB) do { if (smem) k_mega<PATH, COUNT, MINB, true><<<grid, 128, shb, st>>>(ri, g_tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
                                                                                      aov.prim, aov.inst, aov.t, ctr); \
-                                         else k_mega<PATH, COUNT, MINB, false><<<grid, 128, 0, st>>>(ri, sc, P, n_local, tiles_x, m->head, m->b, img, pitch, \
+                                         else k_mega<PATH, COUNT, MINB, false><<<grid, 128, 0, st>>>(ri, g_tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
                                                                                      aov.prim, aov.inst, aov.t, ctr); } while (0)
 #define RTB_MEGA_MB(PATH) do { if (count) RTB_MEGA(PATH, true, 4); else if (mb == 4) RTB_MEGA(PATH, false, 4); else if (mb == 5) RTB_MEGA(PATH, false, 5); \
                                else if (mb == 6) RTB_MEGA(PATH, false, 6); else RTB_MEGA(PATH, false, 8); } while (0)

@@ -25,24 +25,40 @@ def max_rows(height, world):
 
 
 class FrameGather:
-    """Pre-allocated buffers for the per-frame gather; frame is a (H, pitch) uint8 tensor on every rank."""
+    """Pre-allocated buffers for the per-frame gather; frame is a (H, pitch) uint8 tensor on every rank.
+
+    One exchange per frame: every rank r > 0 packs its rows (one index_select) and sends them to rank 0; rank 0 posts
+    all receives as one batched group (a single NCCL group call on GPUs) and scatters everything it received into
+    its frame with one index_select + one index_copy_, whatever the number of ranks."""
 
     def __init__(self, height, pitch, rank, world, device, group=None):
         self.h, self.pitch, self.rank, self.world, self.group = height, pitch, rank, world, group
         self.rows = [rank_rows(height, r, world, device) for r in range(world)]
         n = max_rows(height, world)
-        self.send = torch.zeros((n, pitch), dtype=torch.uint8, device=device)
-        self.recv = [torch.zeros((n, pitch), dtype=torch.uint8, device=device) for _ in range(world)] if rank == 0 else None
+        self.n = n
+        self.send = torch.zeros((n, pitch), dtype=torch.uint8, device=device) if rank != 0 else None
+        self.recv = None
+        if rank == 0 and world > 1:
+            self.recv = torch.zeros((world - 1, n, pitch), dtype=torch.uint8, device=device)
+            src, dst = [], []
+            for r in range(1, world):
+                k = len(self.rows[r])
+                src.append(torch.arange(k, device=device) + (r - 1) * n)
+                dst.append(self.rows[r])
+            self.src_idx = torch.cat(src) if src else None
+            self.dst_rows = torch.cat(dst) if dst else None
 
     def gather(self, frame):
         """After every rank rendered its own bands into `frame`, make rank 0's frame complete."""
         if self.world == 1:
             return frame
-        mine = self.rows[self.rank]
-        self.send[: len(mine)] = frame[mine]
-        dist.gather(self.send, self.recv, dst=0, group=self.group)
-        if self.rank == 0:
-            for r in range(1, self.world):
-                rr = self.rows[r]
-                frame[rr] = self.recv[r][: len(rr)]
+        if self.rank != 0:
+            mine = self.rows[self.rank]
+            torch.index_select(frame, 0, mine, out=self.send[: len(mine)])
+            dist.send(self.send, dst=0, group=self.group)
+            return frame
+        ops = [dist.P2POp(dist.irecv, self.recv[r - 1], r, self.group) for r in range(1, self.world)]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        frame.index_copy_(0, self.dst_rows, self.recv.view(-1, self.pitch).index_select(0, self.src_idx))
         return frame

@@ -34,11 +34,14 @@ def main():
     ref = None
     for combo in itertools.product(*[v for _, v in knobs]):
         for (k, _), v in zip(knobs, combo):
-            scene.set_option(k, v)
+            if k == "tile_count":                           # emulate one rank of an N-GPU run: render 1/N of the bands
+                cam.tile_rank, cam.tile_count = 0, v
+            else:
+                scene.set_option(k, v)
         ms = []
         for i in range(7):
             cam.pose = np.array(bench.camera_pose(cfg, i), np.float32)
-            flush.fill_(i)
+            if not os.environ.get("NOFLUSH"): flush.fill_(i)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             cam.render_scene(scene, frame.data_ptr(), W * 3)
