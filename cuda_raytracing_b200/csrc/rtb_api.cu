@@ -130,6 +130,7 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     else if (n == "key_bits") c->opt_key_bits = value;
     else if (n == "fused") rtb::g_tune.fused = value;
     else if (n == "cost_order") rtb::g_tune.cost_order = value;
+    else if (n == "queue_keep") rtb::g_tune.queue_keep = std::max(1, std::min(value, 33));
     else if (n == "tail_idle") rtb::g_tune.tail_idle = std::max(1, std::min(value, 32));
     else if (n == "spec_thr") rtb::g_tune.spec_thr = std::max(0, std::min(value, 31));
     else if (n == "smem_top") rtb::g_tune.smem_top = std::max(0, std::min(value, 341));

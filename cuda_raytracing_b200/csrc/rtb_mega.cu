@@ -36,6 +36,9 @@ struct MegaState {
     int* head = nullptr;
     unsigned* cost = nullptr;       // per coarse block, accumulated by the frame being rendered
     int* order = nullptr;           // claim order of the blocks for the frame being rendered
+    float4* q_org = nullptr; float4* q_dir = nullptr;   // ray ring of the queue variant (k_megaq)
+    unsigned* q_ticket = nullptr; unsigned* q_ctl = nullptr;
+    size_t q_cap = 0;
     size_t cap = 0;
     int nb_cap = 0;
     // the cost map is only reused when the next frame has the same pixel set
@@ -121,6 +124,114 @@ __global__ void __launch_bounds__(1024) k_order(unsigned* __restrict__ cost, int
 }
 
 // meta word of the ray a lane is tracing: bit 0 = shadow ray, bits 1-7 = bounce, bits 8-31 = sample
+// What retiring a finished ray decided: the next ray of the pixel's chain (`next`) or the end of the pixel (`ended`).
+struct Retired {
+    bool next, ended;
+    f3 o, d, acc;
+    unsigned meta;
+    int x, y, blk;
+};
+
+// Shade the finished ray of pixel slot `idx` (k_shade's arithmetic): closest-hit rays add their unshadowed terms and
+// decide about a shadow ray / continuation, shadow rays add the pending Lambert term and release the continuation.
+// Scratch another SM may have written is read with ld.cg (L2), never through L1.
+template <bool PATH>
+XF Retired retire_ray(const SceneDev& sc, const FrameParams& P, const MegaGeo& G, const MegaBufs& B, int idx, unsigned meta,
+                      float hmin, f3 ray_dir, f3 L, int32_t* __restrict__ aov_prim, int32_t* __restrict__ aov_inst,
+                      float* __restrict__ aov_t)
+{
+    Retired R;
+    int x, y, blk;
+    slot_to_pixel(P, G, idx, x, y, blk);
+    R.x = x; R.y = y; R.blk = blk;
+    const int pix = y * P.width + x;
+    const int bounce = (int)((meta >> 1) & 127u), sample = (int)(meta >> 8);
+    bool next = false, ended = false;
+    f3 no = mk3(0.f, 0.f, 0.f), nd = no, acc = no;
+    unsigned nmeta = 0;
+    if (meta & 1u) {
+        // shadow ray done.  commented block raycast.cu:262-290: illumination = 0.4 cos, or cos when the light is visible
+        const float4 p0 = __ldcg(B.sp0 + idx), p1 = __ldcg(B.sp1 + idx), a = __ldcg(B.acc + idx), co = __ldcg(B.cont_o + idx);
+        float il = hmin == FLT_MAX ? p1.w : __double2float_rn(__dmul_rn(0.4, (double)p1.w));
+        il = fmaxf(0.4f, fminf(1.0f, il));
+        acc = mk3(xa(a.x, xm(p0.x, xm(p0.w, xm(il, p1.x)))), xa(a.y, xm(p0.y, xm(p0.w, xm(il, p1.y)))),
+                  xa(a.z, xm(p0.z, xm(p0.w, xm(il, p1.z)))));
+        if (co.w != 0.0f) {
+            const float4 cd = __ldcg(B.cont_d + idx);
+            next = true; no = mk3(co.x, co.y, co.z); nd = mk3(cd.x, cd.y, cd.z);
+            nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1);
+        } else ended = true;
+    } else {
+        f3 thr = mk3(1.f, 1.f, 1.f);
+        if (bounce > 0) { const float4 t4 = __ldcg(B.thr + idx); thr = mk3(t4.x, t4.y, t4.z); }
+        if (bounce > 0 || (PATH && sample > 0)) { const float4 a4 = __ldcg(B.acc + idx); acc = mk3(a4.x, a4.y, a4.z); }
+        Hit h;
+        h.min = hmin; h.prim = -1; h.inst = -1;
+        if (h.min == FLT_MAX) {
+            acc = mk3(xa(acc.x, xm(thr.x, c_sky[0])), xa(acc.y, xm(thr.y, c_sky[1])), xa(acc.z, xm(thr.z, c_sky[2])));
+            ended = true;
+        } else {
+            const float4 h0 = B.hit0[idx], h1 = B.hit1[idx];
+            h.u = h0.y; h.v = h0.z; h.inst = __float_as_int(h0.w);
+            h.loc = mk3(h1.x, h1.y, h1.z); h.slot = __float_as_int(h1.w);
+            InstXf xf;
+            load_instance(sc.inst, h.inst, xf);
+            const float4 q0 = __ldg(sc.meshes[xf.mesh].tris + (size_t)h.slot * TRI_F4);
+            h.prim = __float_as_int(q0.w);
+            const f3 c = base_colour(sc, h, xf.material, xf.mesh);
+            const f3 nrm = xnormalize(xmul3(xapply_quat(xf.q_inv, mk3(q0.x, q0.y, q0.z)), xf.scale));   // raycast.cu:115-122
+            if (!PATH) {
+                const float m = sc.materials[xf.material].metallic;
+                const float w = xs(1.0f, m);
+                const float cosl = xdot(nrm, L);
+                const bool cont = m > 0.0f && bounce < P.max_depth;
+                f3 cdir = mk3(0.f, 0.f, 0.f), corg = cdir;
+                if (cont) {
+                    cdir = reflect_dir(ray_dir, nrm);
+                    corg = xadd(h.loc, xscale(cdir, 1e-4f));
+                    B.thr[idx] = make_float4(xm(thr.x, xm(m, c.x)), xm(thr.y, xm(m, c.y)), xm(thr.z, xm(m, c.z)), 0.f);
+                }
+                if (cosl > 0.0f) {          // raycast.cu:268: the Lambert term waits for the shadow ray
+                    B.sp0[idx] = make_float4(thr.x, thr.y, thr.z, w);
+                    B.sp1[idx] = make_float4(c.x, c.y, c.z, cosl);
+                    B.cont_o[idx] = make_float4(corg.x, corg.y, corg.z, cont ? 1.0f : 0.0f);
+                    if (cont) B.cont_d[idx] = make_float4(cdir.x, cdir.y, cdir.z, 0.f);
+                    next = true; no = xadd(h.loc, xscale(L, 1e-4f)); nd = L;              // raycast.cu:259
+                    nmeta = meta | 1u;
+                } else {
+                    const float il = fmaxf(0.4f, fminf(1.0f, __double2float_rn(__dmul_rn(0.4, (double)cosl))));
+                    acc = mk3(xa(acc.x, xm(thr.x, xm(w, xm(il, c.x)))), xa(acc.y, xm(thr.y, xm(w, xm(il, c.y)))),
+                              xa(acc.z, xm(thr.z, xm(w, xm(il, c.z)))));
+                    if (cont) { next = true; no = corg; nd = cdir; nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1); }
+                    else ended = true;
+                }
+            } else {
+                thr = mk3(xm(thr.x, c.x), xm(thr.y, c.y), xm(thr.z, c.z));
+                if (bounce < P.max_depth) {
+                    unsigned r4[4] = { (unsigned)pix, (unsigned)sample, (unsigned)(bounce + 1), 0u };
+                    philox4x32(r4, P.seed, 0x5eed5eedu);
+                    nd = cosine_dir(nrm, u01(r4[0]), u01(r4[1]));
+                    no = xadd(h.loc, xscale(nd, 1e-4f));
+                    B.thr[idx] = make_float4(thr.x, thr.y, thr.z, 0.f);
+                    next = true; nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1);
+                } else ended = true;
+            }
+        }
+        if (!PATH && bounce == 0) {
+            if (aov_prim) aov_prim[pix] = h.prim;
+            if (aov_inst) aov_inst[pix] = h.inst;
+            if (aov_t) aov_t[pix] = h.min;
+        }
+    }
+    if (ended && PATH && sample + 1 < P.spp) {          // next sample of the same pixel
+        ended = false; next = true;
+        no = mk3(P.ox, P.oy, P.oz); nd = camera_ray(P, x, y, sample + 1, true);
+        nmeta = (unsigned)(sample + 1) << 8;
+    }
+    R.next = next; R.ended = ended; R.o = no; R.d = nd; R.acc = acc; R.meta = nmeta;
+    return R;
+}
+
 template <bool PATH, bool COUNT, int MINB, bool SMEM>
 __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_idle, SceneDev sc, FrameParams P, MegaGeo G,
                                                     int* __restrict__ head, MegaBufs B, unsigned char* __restrict__ img, size_t pitch,
@@ -148,92 +259,11 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
         const bool idle = S.cur == EMPTY_REF;
         // ---------------- retire the finished ray of every idle lane: shade, continue the chain or end the pixel
         if (idle && idx >= 0) {
-            int x, y, blk;
-            slot_to_pixel(P, G, idx, x, y, blk);
-            const int pix = y * P.width + x;
-            const int bounce = (int)((meta >> 1) & 127u), sample = (int)(meta >> 8);
-            bool next = false, ended = false;
-            f3 no = mk3(0.f, 0.f, 0.f), nd = no, acc = no;
-            unsigned nmeta = 0;
-            if (meta & 1u) {
-                // shadow ray done.  commented block raycast.cu:262-290: illumination = 0.4 cos, or cos when the light is visible
-                const float4 p0 = B.sp0[idx], p1 = B.sp1[idx], a = B.acc[idx], co = B.cont_o[idx];
-                float il = sink.hmin == FLT_MAX ? p1.w : __double2float_rn(__dmul_rn(0.4, (double)p1.w));
-                il = fmaxf(0.4f, fminf(1.0f, il));
-                acc = mk3(xa(a.x, xm(p0.x, xm(p0.w, xm(il, p1.x)))), xa(a.y, xm(p0.y, xm(p0.w, xm(il, p1.y)))),
-                          xa(a.z, xm(p0.z, xm(p0.w, xm(il, p1.z)))));
-                if (co.w != 0.0f) {
-                    const float4 cd = B.cont_d[idx];
-                    next = true; no = mk3(co.x, co.y, co.z); nd = mk3(cd.x, cd.y, cd.z);
-                    nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1);
-                } else ended = true;
-            } else {
-                f3 thr = mk3(1.f, 1.f, 1.f);
-                if (bounce > 0) { const float4 t4 = B.thr[idx]; thr = mk3(t4.x, t4.y, t4.z); }
-                if (bounce > 0 || (PATH && sample > 0)) { const float4 a4 = B.acc[idx]; acc = mk3(a4.x, a4.y, a4.z); }
-                Hit h;
-                h.min = sink.hmin; h.prim = -1; h.inst = -1;
-                if (h.min == FLT_MAX) {
-                    acc = mk3(xa(acc.x, xm(thr.x, c_sky[0])), xa(acc.y, xm(thr.y, c_sky[1])), xa(acc.z, xm(thr.z, c_sky[2])));
-                    ended = true;
-                } else {
-                    const float4 h0 = B.hit0[idx], h1 = B.hit1[idx];
-                    h.u = h0.y; h.v = h0.z; h.inst = __float_as_int(h0.w);
-                    h.loc = mk3(h1.x, h1.y, h1.z); h.slot = __float_as_int(h1.w);
-                    InstXf xf;
-                    load_instance(sc.inst, h.inst, xf);
-                    const float4 q0 = __ldg(sc.meshes[xf.mesh].tris + (size_t)h.slot * TRI_F4);
-                    h.prim = __float_as_int(q0.w);
-                    const f3 c = base_colour(sc, h, xf.material, xf.mesh);
-                    const f3 nrm = xnormalize(xmul3(xapply_quat(xf.q_inv, mk3(q0.x, q0.y, q0.z)), xf.scale));   // raycast.cu:115-122
-                    if (!PATH) {
-                        const float m = sc.materials[xf.material].metallic;
-                        const float w = xs(1.0f, m);
-                        const float cosl = xdot(nrm, L);
-                        const bool cont = m > 0.0f && bounce < P.max_depth;
-                        f3 cdir = mk3(0.f, 0.f, 0.f), corg = cdir;
-                        if (cont) {
-                            cdir = reflect_dir(S.dir, nrm);
-                            corg = xadd(h.loc, xscale(cdir, 1e-4f));
-                            B.thr[idx] = make_float4(xm(thr.x, xm(m, c.x)), xm(thr.y, xm(m, c.y)), xm(thr.z, xm(m, c.z)), 0.f);
-                        }
-                        if (cosl > 0.0f) {          // raycast.cu:268: the Lambert term waits for the shadow ray
-                            B.sp0[idx] = make_float4(thr.x, thr.y, thr.z, w);
-                            B.sp1[idx] = make_float4(c.x, c.y, c.z, cosl);
-                            B.cont_o[idx] = make_float4(corg.x, corg.y, corg.z, cont ? 1.0f : 0.0f);
-                            if (cont) B.cont_d[idx] = make_float4(cdir.x, cdir.y, cdir.z, 0.f);
-                            next = true; no = xadd(h.loc, xscale(L, 1e-4f)); nd = L;              // raycast.cu:259
-                            nmeta = meta | 1u;
-                        } else {
-                            const float il = fmaxf(0.4f, fminf(1.0f, __double2float_rn(__dmul_rn(0.4, (double)cosl))));
-                            acc = mk3(xa(acc.x, xm(thr.x, xm(w, xm(il, c.x)))), xa(acc.y, xm(thr.y, xm(w, xm(il, c.y)))),
-                                      xa(acc.z, xm(thr.z, xm(w, xm(il, c.z)))));
-                            if (cont) { next = true; no = corg; nd = cdir; nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1); }
-                            else ended = true;
-                        }
-                    } else {
-                        thr = mk3(xm(thr.x, c.x), xm(thr.y, c.y), xm(thr.z, c.z));
-                        if (bounce < P.max_depth) {
-                            unsigned r4[4] = { (unsigned)pix, (unsigned)sample, (unsigned)(bounce + 1), 0u };
-                            philox4x32(r4, P.seed, 0x5eed5eedu);
-                            nd = cosine_dir(nrm, u01(r4[0]), u01(r4[1]));
-                            no = xadd(h.loc, xscale(nd, 1e-4f));
-                            B.thr[idx] = make_float4(thr.x, thr.y, thr.z, 0.f);
-                            next = true; nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1);
-                        } else ended = true;
-                    }
-                }
-                if (!PATH && bounce == 0) {
-                    if (aov_prim) aov_prim[pix] = h.prim;
-                    if (aov_inst) aov_inst[pix] = h.inst;
-                    if (aov_t) aov_t[pix] = h.min;
-                }
-            }
-            if (ended && PATH && sample + 1 < P.spp) {          // next sample of the same pixel
-                ended = false; next = true;
-                no = mk3(P.ox, P.oy, P.oz); nd = camera_ray(P, x, y, sample + 1, true);
-                nmeta = (unsigned)(sample + 1) << 8;
-            }
+            const Retired R = retire_ray<PATH>(sc, P, G, B, idx, meta, sink.hmin, S.dir, L, aov_prim, aov_inst, aov_t);
+            const bool next = R.next, ended = R.ended;
+            const f3 no = R.o, nd = R.d, acc = R.acc;
+            const unsigned nmeta = R.meta;
+            const int x = R.x, y = R.y, blk = R.blk;
             if (next) {
                 B.acc[idx] = make_float4(acc.x, acc.y, acc.z, 0.f);
                 meta = nmeta;
@@ -291,6 +321,183 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
     if (lane == 0 && rays) atomicAdd(&ctr->rays, (unsigned long long)rays);
 }
 
+
+// ------------------------------------------------------------------ fused kernel with in-kernel ray queues
+// Same chain semantics as k_mega, but a ray produced while shading is not traced by the lane that produced it: it is
+// appended to a ring in HBM (warp-ballot compaction, one atomicAdd per warp) and warps always start 32 rays at once --
+// the next 32 queued rays when a ring holds a warp's worth, else a fresh 8x4 pixel tile.  Deep bounces, which leave a
+// tile with 1-4 live lanes in k_mega, run in full warps again, and it is still ONE launch per frame.
+//   * QR_RINGS rings; a CTA produces into ring (blockIdx % QR_RINGS) and consumes from it first, then from the next
+//     few, so the head/tail words are shared by ~10 CTAs instead of all 1184 (one global ring livelocks on its CAS).
+//   * producers reserve slots with atomicAdd(tail), write the 32-byte entry, fence, publish ticket[slot] = position+1;
+//     consumers reserve with atomicCAS(head) only below the tail they read, spin on the ticket, fence, read with ld.cg.
+//   * a full ring never blocks: the producing lanes keep their rays and trace them themselves (k_mega's behaviour).
+//   * once every tile is claimed nothing is enqueued any more (the frame tail is latency-bound: a queue hop only delays
+//     the chain); a warp leaves when no tile is unclaimed and every ring is empty.  A ray enqueued concurrently with that
+//     check is never stranded: its producer passes through the fetch path right after the enqueue and finds it.
+constexpr int QR_RINGS = 128;
+constexpr int QR_CTL = 64;                      // unsigned words per ring control block: [0] head, [32] tail (separate lines)
+struct QRing {
+    float4* org;                    // [QR_RINGS][cap] (origin, pixel slot)
+    float4* dir;                    // [QR_RINGS][cap] (direction, meta)
+    unsigned* ticket;               // [QR_RINGS][cap]
+    unsigned* ctl;                  // [QR_RINGS][QR_CTL]
+    unsigned* pending;
+    unsigned cap;                   // entries per ring, power of two
+};
+
+XF unsigned ld_volatile_u32(const unsigned* p) { return *(const volatile unsigned*)p; }
+
+// leader-only: try to reserve up to 32 entries of ring r; returns the count (0 = nothing / lost the race), base in `h`
+XF int ring_try_claim(const QRing& Q, int r, bool any, unsigned& h)
+{
+    unsigned* c = Q.ctl + (size_t)r * QR_CTL;
+    h = ld_volatile_u32(c);
+    const int avail = (int)(ld_volatile_u32(c + 32) - h);
+    if (avail >= 32 || (any && avail > 0)) {
+        const int n = min(32, avail);
+        if (atomicCAS(c, h, h + (unsigned)n) == h) return n;
+    }
+    return 0;
+}
+
+template <bool PATH, bool COUNT, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, FrameParams P, MegaGeo G, int* __restrict__ head, QRing Q, MegaBufs B,
+                                                     unsigned char* __restrict__ img, size_t pitch, int32_t* __restrict__ aov_prim,
+                                                     int32_t* __restrict__ aov_inst, float* __restrict__ aov_t, Counters* ctr)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const int r0 = blockIdx.x % QR_RINGS;
+    const f3 L = mk3(P.light_dir.x, P.light_dir.y, P.light_dir.z);
+    TopLevels T;
+    T.n_tlas = T.n_blas = 0; T.s_tlas = T.s_blas = T.g_blas = nullptr;
+    RTB_DECL_STACK(stk);
+    TraceState S;
+    MegaSink sink;
+    sink.h0 = B.hit0; sink.h1 = B.hit1;
+    sink.reset(-1, false);
+    S.clear();
+    int idx = -1;
+    unsigned meta = 0;
+    bool more = true;                           // warp-uniform: unclaimed pixel tiles may remain
+    unsigned rays = 0;
+    for (;;) {
+        // ---------------- every lane is idle here: retire the generation that just finished
+        bool next = false, ended = false;
+        f3 no = mk3(0.f, 0.f, 0.f), nd = no;
+        unsigned nmeta = 0;
+        if (idx >= 0) {
+            const Retired R = retire_ray<PATH>(sc, P, G, B, idx, meta, sink.hmin, S.dir, L, aov_prim, aov_inst, aov_t);
+            next = R.next; ended = R.ended; no = R.o; nd = R.d; nmeta = R.meta;
+            if (next) B.acc[idx] = make_float4(R.acc.x, R.acc.y, R.acc.z, 0.f);
+            if (ended) {                                        // radiance -> 8-bit BGR pixel (PATH: mean over samples)
+                const float scale = PATH ? 1.0f / (float)P.spp : 1.0f;
+                unsigned char* p = img + (size_t)R.y * pitch + 3 * (size_t)R.x;
+                p[0] = to_u8(xm(clamp01(xm(R.acc.x, scale)), 255.0f));
+                p[1] = to_u8(xm(clamp01(xm(R.acc.y, scale)), 255.0f));
+                p[2] = to_u8(xm(clamp01(xm(R.acc.z, scale)), 255.0f));
+            }
+        }
+        const unsigned nm = __ballot_sync(0xffffffffu, next);
+        bool kept = false;                                      // warp-uniform: the rays stayed in their lanes (ring full)
+        if (nm) {                                               // append the continuing rays: one atomic per warp
+            const int leader = __ffs(nm) - 1;
+            unsigned base = 0xffffffffu;
+            // a generation that stays wide enough keeps its lanes; so does every generation once the tiles are gone (the
+            // frame tail is latency-bound: a queue hop only delays the chain)
+            if (lane == leader && __popc(nm) < keep_thr && *(volatile int*)head < G.n_slots) {
+                unsigned* c = Q.ctl + (size_t)r0 * QR_CTL;
+                const unsigned used = ld_volatile_u32(c + 32) - ld_volatile_u32(c);
+                if (used + 4096u <= Q.cap) base = atomicAdd(c + 32, (unsigned)__popc(nm));   // margin > every sharing warp's 32
+            }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            kept = base == 0xffffffffu;
+            if (next) {
+                if (!kept) {
+                    const unsigned pos = base + __popc(nm & lt), slot = pos & (Q.cap - 1u);
+                    const size_t e = (size_t)r0 * Q.cap + slot;
+                    Q.org[e] = make_float4(no.x, no.y, no.z, __int_as_float(idx));
+                    Q.dir[e] = make_float4(nd.x, nd.y, nd.z, __uint_as_float(nmeta));
+                    __threadfence();
+                    *(volatile unsigned*)(Q.ticket + e) = pos + 1u;
+                } else {
+                    meta = nmeta;
+                    sink.reset(idx, (nmeta & 1u) != 0u);
+                    S.begin(sc, no, nd, stk);
+                    rays++;
+                }
+            }
+        }
+        if (!(kept && next)) idx = -1;
+        if (!kept) {
+            // ---------------- get the next 32 rays: queued rays when a ring holds a warp's worth, else a new tile; once the
+            // tiles are gone take whatever any ring still holds, and leave when every ring is empty (a ray enqueued after that
+            // is picked up by its own producer, which always passes through here after an enqueue)
+            int got = 0, qr = 0, qn = 0, pbase = 0;             // got: 1 = ring qr entries [qbase, qbase + qn), 2 = pixel slots, 3 = done
+            unsigned qbase = 0;
+            for (int tries = 0; !got; tries++) {
+                if (more) {
+                    if (lane == 0) {
+                        for (int k = 0; k < 4 && !got; k++) {   // own ring, then three neighbours
+                            const int r = (r0 + k) % QR_RINGS;
+                            qn = ring_try_claim(Q, r, false, qbase);
+                            if (qn) { got = 1; qr = r; }
+                        }
+                        if (!got) { pbase = atomicAdd(head, 32); got = 2; }
+                    }
+                } else {
+                    bool has = false; int mine = 0;             // every lane looks at QR_RINGS / 32 rings
+                    for (int k = 0; k < QR_RINGS / 32 && !has; k++) {
+                        mine = (r0 + lane + 32 * k) % QR_RINGS;
+                        const unsigned* c = Q.ctl + (size_t)mine * QR_CTL;
+                        has = (int)(ld_volatile_u32(c + 32) - ld_volatile_u32(c)) > 0;
+                    }
+                    const unsigned hm = __ballot_sync(0xffffffffu, has);
+                    const int any_r = hm ? __shfl_sync(0xffffffffu, mine, __ffs(hm) - 1) : -1;
+                    if (lane == 0) {
+                        if (any_r < 0 || tries > (1 << 16)) got = 3;
+                        else { qn = ring_try_claim(Q, any_r, true, qbase); if (qn) { got = 1; qr = any_r; } }
+                    }
+                }
+                got = __shfl_sync(0xffffffffu, got, 0);
+            }
+            if (got == 3) break;
+            if (got == 1) {
+                qbase = __shfl_sync(0xffffffffu, qbase, 0); qn = __shfl_sync(0xffffffffu, qn, 0); qr = __shfl_sync(0xffffffffu, qr, 0);
+                if (lane < qn) {
+                    const unsigned pos = qbase + (unsigned)lane, slot = pos & (Q.cap - 1u);
+                    const size_t e = (size_t)qr * Q.cap + slot;
+                    unsigned wait = 0;
+                    while (ld_volatile_u32(Q.ticket + e) != pos + 1u) { if (++wait > (1u << 26)) { ctr->overflow = 1; break; } }
+                    __threadfence();
+                    const float4 o = __ldcg(Q.org + e), d = __ldcg(Q.dir + e);
+                    idx = __float_as_int(o.w); meta = __float_as_uint(d.w);
+                    sink.reset(idx, (meta & 1u) != 0u);
+                    S.begin(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), stk);
+                    rays++;
+                }
+            } else {
+                pbase = __shfl_sync(0xffffffffu, pbase, 0);
+                const int i = pbase + lane;
+                int x, y, blk;
+                const bool valid = i < G.n_slots && slot_to_pixel(P, G, i, x, y, blk);
+                if (valid) {
+                    idx = i; meta = 0;
+                    sink.reset(idx, false);
+                    S.begin(sc, mk3(P.ox, P.oy, P.oz), camera_ray(P, x, y, 0, PATH), stk);
+                    rays++;
+                }
+                if (pbase + 32 >= G.n_slots) more = false;
+            }
+        }
+        while (__any_sync(0xffffffffu, S.cur != EMPTY_REF)) S.template advance<false, COUNT, false>(sc, stk, sink, T);
+    }
+    S.template flush_counters<COUNT>(ctr);
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
+    if (lane == 0 && rays) atomicAdd(&ctr->rays, (unsigned long long)rays);
+}
+
 #define MCK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 
 static void mega_free(MegaState* m)
@@ -300,6 +507,11 @@ static void mega_free(MegaState* m)
     if (m->head) cudaFree(m->head);
     if (m->cost) cudaFree(m->cost);
     if (m->order) cudaFree(m->order);
+    if (m->q_org) cudaFree(m->q_org);
+    if (m->q_dir) cudaFree(m->q_dir);
+    if (m->q_ticket) cudaFree(m->q_ticket);
+    if (m->q_ctl) cudaFree(m->q_ctl);
+    m->q_org = m->q_dir = nullptr; m->q_ticket = m->q_ctl = nullptr; m->q_cap = 0;
     m->head = nullptr; m->cost = nullptr; m->order = nullptr; m->cap = 0; m->nb_cap = 0; m->hist_rank = -1;
 }
 
@@ -361,6 +573,35 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
     const int grid = std::min(sms * (count ? 4 : mb), (G.n_slots + 127) / 128);
     const bool smem = sc.top_tlas_n + sc.top_blas_n > 0;
     const size_t shb = smem ? (size_t)(sc.top_tlas_n + sc.top_blas_n) * 128 + 16 : 0;
+    if (g_tune.fused == 2) {                                            // in-kernel ray queue variant
+        size_t qcap = 8192;                                             // entries per ring; a full ring falls back to in-lane tracing
+        while (qcap * QR_RINGS < 2 * (size_t)G.n_slots) qcap <<= 1;
+        if (m->q_cap < qcap) {
+            if (m->q_org) cudaFree(m->q_org);
+            if (m->q_dir) cudaFree(m->q_dir);
+            if (m->q_ticket) cudaFree(m->q_ticket);
+            if (m->q_ctl) cudaFree(m->q_ctl);
+            m->q_org = m->q_dir = nullptr; m->q_ticket = m->q_ctl = nullptr; m->q_cap = 0;
+            MCK(cudaMalloc((void**)&m->q_org, sizeof(float4) * qcap * QR_RINGS));
+            MCK(cudaMalloc((void**)&m->q_dir, sizeof(float4) * qcap * QR_RINGS));
+            MCK(cudaMalloc((void**)&m->q_ticket, sizeof(unsigned) * qcap * QR_RINGS));
+            MCK(cudaMalloc((void**)&m->q_ctl, sizeof(unsigned) * (QR_RINGS * QR_CTL + 32)));
+            m->q_cap = qcap;
+        }
+        MCK(cudaMemsetAsync(m->q_ticket, 0, sizeof(unsigned) * m->q_cap * QR_RINGS, st));
+        MCK(cudaMemsetAsync(m->q_ctl, 0, sizeof(unsigned) * (QR_RINGS * QR_CTL + 32), st));
+        QRing Q;
+        Q.org = m->q_org; Q.dir = m->q_dir; Q.ticket = m->q_ticket; Q.ctl = m->q_ctl; Q.pending = m->q_ctl + QR_RINGS * QR_CTL;
+        Q.cap = (unsigned)m->q_cap;
+        MegaGeo GQ = G;
+        GQ.order = nullptr;                                             // no cost map in this variant
+#define RTB_MEGAQ(PATH, COUNT, MINB) k_megaq<PATH, COUNT, MINB><<<grid, 128, 0, st>>>(g_tune.queue_keep, sc, P, GQ, m->head, Q, m->b, img, pitch, aov.prim, aov.inst, aov.t, ctr)
+#define RTB_MEGAQ_MB(PATH) do { if (count) RTB_MEGAQ(PATH, true, 4); else if (mb <= 5) RTB_MEGAQ(PATH, false, 5); \
+                                else if (mb == 6) RTB_MEGAQ(PATH, false, 6); else RTB_MEGAQ(PATH, false, 8); } while (0)
+        if (path) RTB_MEGAQ_MB(true); else RTB_MEGAQ_MB(false);
+        g_wave_launches++;
+        return cudaGetLastError();
+    }
 #define RTB_MEGA(PATH, COUNT, MINB) do { if (smem) k_mega<PATH, COUNT, MINB, true><<<grid, 128, shb, st>>>(ri, g_tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
                                                                                      aov.prim, aov.inst, aov.t, ctr); \
                                          else k_mega<PATH, COUNT, MINB, false><<<grid, 128, 0, st>>>(ri, g_tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
