@@ -274,9 +274,9 @@ class Scene:
         return {f: (list(getattr(info, f)) if f.startswith("bounds") else getattr(info, f)) for f, _ in MeshInfo._fields_}
 
     def mesh_arrays(self, index):
-        """Download the wide nodes (N,8,4 float32), triangle records (T,4,4 float32) and leaf order (T uint32)."""
+        """Download the wide nodes (N,7,4 float32), triangle records (T,4,4 float32) and leaf order (T uint32)."""
         info = self.mesh_info(index)
-        nodes = np.zeros((info["num_nodes"], 8, 4), np.float32)
+        nodes = np.zeros((info["num_nodes"], 7, 4), np.float32)
         tris = np.zeros((info["num_triangles"], 4, 4), np.float32)
         order = np.zeros(info["num_triangles"], np.uint32)
         for what, arr in ((0, nodes), (1, tris), (2, order)):

@@ -275,7 +275,6 @@ __global__ void __launch_bounds__(128) k_collapse(int level, const int2* __restr
         nd[2] = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]); nd[3] = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
         nd[4] = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd[5] = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
         nd[6] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), __int_as_float(ref[2]), __int_as_float(ref[3]));
-        nd[7] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (my_leaves) { atomicAdd(&c->n_leaves, my_leaves); atomicMax(&c->max_leaf, my_maxleaf); atomicMax(&c->max_level, level); }
 }
@@ -289,7 +288,7 @@ __global__ void k_trivial_root(float4* nodes, const float4* bmin, const float4* 
     int ref0 = EMPTY_REF;
     if (n == 1) { lx.x = bmin[0].x; ly.x = bmin[0].y; lz.x = bmin[0].z; hx.x = bmax[0].x; hy.x = bmax[0].y; hz.x = bmax[0].z; ref0 = ~0; }
     nodes[0] = lx; nodes[1] = hx; nodes[2] = ly; nodes[3] = hy; nodes[4] = lz; nodes[5] = hz;
-    nodes[6] = make_float4(__int_as_float(ref0), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF)); nodes[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+    nodes[6] = make_float4(__int_as_float(ref0), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF));
 }
 
 __global__ void k_iota(unsigned* v, int n) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) v[i] = i; }

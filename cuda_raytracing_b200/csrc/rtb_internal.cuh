@@ -24,7 +24,10 @@
 
 namespace rtb {
 
-constexpr int NODE_F4 = 8;          // float4 per wide node
+// float4 per wide node.  7, not 8: with a 128-byte stride every lane of a warp reads field k of ITS node from the same four
+// L1 banks (32-way conflict, 32 cycles per LDG.128: tools/l1_probe.cu); a 112-byte stride puts field k of node n in bank
+// group (k - n) mod 8, so lanes on different nodes spread over all banks.
+constexpr int NODE_F4 = 7;
 constexpr int TRI_F4 = 4;           // float4 per triangle record
 constexpr int INST_F4 = 6;          // float4 per instance record
 constexpr int MAX_LEAF = 8;         // triangles per leaf (3-bit count)

@@ -58,8 +58,8 @@ struct MegaSink {
     {
         hmin = distance; hinst = inst; hprim = prim;
         if (!shadow) {
-            h0[idx] = make_float4(distance, u, v, __int_as_float(inst));
-            h1[idx] = make_float4(loc.x, loc.y, loc.z, __int_as_float(slot));
+            st_stream(h0 + idx, make_float4(distance, u, v, __int_as_float(inst)));
+            st_stream(h1 + idx, make_float4(loc.x, loc.y, loc.z, __int_as_float(slot)));
         }
     }
 };
@@ -151,32 +151,32 @@ XF Retired retire_ray(const SceneDev& sc, const FrameParams& P, const MegaGeo& G
     unsigned nmeta = 0;
     if (meta & 1u) {
         // shadow ray done.  commented block raycast.cu:262-290: illumination = 0.4 cos, or cos when the light is visible
-        const float4 p0 = __ldcg(B.sp0 + idx), p1 = __ldcg(B.sp1 + idx), a = __ldcg(B.acc + idx), co = __ldcg(B.cont_o + idx);
+        const float4 p0 = ld_stream(B.sp0 + idx), p1 = ld_stream(B.sp1 + idx), a = ld_stream(B.acc + idx), co = ld_stream(B.cont_o + idx);
         float il = hmin == FLT_MAX ? p1.w : __double2float_rn(__dmul_rn(0.4, (double)p1.w));
         il = fmaxf(0.4f, fminf(1.0f, il));
         acc = mk3(xa(a.x, xm(p0.x, xm(p0.w, xm(il, p1.x)))), xa(a.y, xm(p0.y, xm(p0.w, xm(il, p1.y)))),
                   xa(a.z, xm(p0.z, xm(p0.w, xm(il, p1.z)))));
         if (co.w != 0.0f) {
-            const float4 cd = __ldcg(B.cont_d + idx);
+            const float4 cd = ld_stream(B.cont_d + idx);
             next = true; no = mk3(co.x, co.y, co.z); nd = mk3(cd.x, cd.y, cd.z);
             nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1);
         } else ended = true;
     } else {
         f3 thr = mk3(1.f, 1.f, 1.f);
-        if (bounce > 0) { const float4 t4 = __ldcg(B.thr + idx); thr = mk3(t4.x, t4.y, t4.z); }
-        if (bounce > 0 || (PATH && sample > 0)) { const float4 a4 = __ldcg(B.acc + idx); acc = mk3(a4.x, a4.y, a4.z); }
+        if (bounce > 0) { const float4 t4 = ld_stream(B.thr + idx); thr = mk3(t4.x, t4.y, t4.z); }
+        if (bounce > 0 || (PATH && sample > 0)) { const float4 a4 = ld_stream(B.acc + idx); acc = mk3(a4.x, a4.y, a4.z); }
         Hit h;
         h.min = hmin; h.prim = -1; h.inst = -1;
         if (h.min == FLT_MAX) {
             acc = mk3(xa(acc.x, xm(thr.x, c_sky[0])), xa(acc.y, xm(thr.y, c_sky[1])), xa(acc.z, xm(thr.z, c_sky[2])));
             ended = true;
         } else {
-            const float4 h0 = B.hit0[idx], h1 = B.hit1[idx];
+            const float4 h0 = ld_stream(B.hit0 + idx), h1 = ld_stream(B.hit1 + idx);
             h.u = h0.y; h.v = h0.z; h.inst = __float_as_int(h0.w);
             h.loc = mk3(h1.x, h1.y, h1.z); h.slot = __float_as_int(h1.w);
             InstXf xf;
             load_instance(sc.inst, h.inst, xf);
-            const float4 q0 = __ldg(sc.meshes[xf.mesh].tris + (size_t)h.slot * TRI_F4);
+            const float4 q0 = ld_keep(sc.meshes[xf.mesh].tris + (size_t)h.slot * TRI_F4);
             h.prim = __float_as_int(q0.w);
             const f3 c = base_colour(sc, h, xf.material, xf.mesh);
             const f3 nrm = xnormalize(xmul3(xapply_quat(xf.q_inv, mk3(q0.x, q0.y, q0.z)), xf.scale));   // raycast.cu:115-122
@@ -189,13 +189,13 @@ XF Retired retire_ray(const SceneDev& sc, const FrameParams& P, const MegaGeo& G
                 if (cont) {
                     cdir = reflect_dir(ray_dir, nrm);
                     corg = xadd(h.loc, xscale(cdir, 1e-4f));
-                    B.thr[idx] = make_float4(xm(thr.x, xm(m, c.x)), xm(thr.y, xm(m, c.y)), xm(thr.z, xm(m, c.z)), 0.f);
+                    st_stream(B.thr + idx, make_float4(xm(thr.x, xm(m, c.x)), xm(thr.y, xm(m, c.y)), xm(thr.z, xm(m, c.z)), 0.f));
                 }
                 if (cosl > 0.0f) {          // raycast.cu:268: the Lambert term waits for the shadow ray
-                    B.sp0[idx] = make_float4(thr.x, thr.y, thr.z, w);
-                    B.sp1[idx] = make_float4(c.x, c.y, c.z, cosl);
-                    B.cont_o[idx] = make_float4(corg.x, corg.y, corg.z, cont ? 1.0f : 0.0f);
-                    if (cont) B.cont_d[idx] = make_float4(cdir.x, cdir.y, cdir.z, 0.f);
+                    st_stream(B.sp0 + idx, make_float4(thr.x, thr.y, thr.z, w));
+                    st_stream(B.sp1 + idx, make_float4(c.x, c.y, c.z, cosl));
+                    st_stream(B.cont_o + idx, make_float4(corg.x, corg.y, corg.z, cont ? 1.0f : 0.0f));
+                    if (cont) st_stream(B.cont_d + idx, make_float4(cdir.x, cdir.y, cdir.z, 0.f));
                     next = true; no = xadd(h.loc, xscale(L, 1e-4f)); nd = L;              // raycast.cu:259
                     nmeta = meta | 1u;
                 } else {
@@ -212,7 +212,7 @@ XF Retired retire_ray(const SceneDev& sc, const FrameParams& P, const MegaGeo& G
                     philox4x32(r4, P.seed, 0x5eed5eedu);
                     nd = cosine_dir(nrm, u01(r4[0]), u01(r4[1]));
                     no = xadd(h.loc, xscale(nd, 1e-4f));
-                    B.thr[idx] = make_float4(thr.x, thr.y, thr.z, 0.f);
+                    st_stream(B.thr + idx, make_float4(thr.x, thr.y, thr.z, 0.f));
                     next = true; nmeta = (meta & ~255u) | ((unsigned)(bounce + 1) << 1);
                 } else ended = true;
             }
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
             const unsigned nmeta = R.meta;
             const int x = R.x, y = R.y, blk = R.blk;
             if (next) {
-                B.acc[idx] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                st_stream(B.acc + idx, make_float4(acc.x, acc.y, acc.z, 0.f));
                 meta = nmeta;
                 sink.reset(idx, (nmeta & 1u) != 0u);
                 S.begin(sc, no, nd, stk);
@@ -342,7 +342,6 @@ struct QRing {
     float4* dir;                    // [QR_RINGS][cap] (direction, meta)
     unsigned* ticket;               // [QR_RINGS][cap]
     unsigned* ctl;                  // [QR_RINGS][QR_CTL]
-    unsigned* pending;
     unsigned cap;                   // entries per ring, power of two
 };
 
@@ -390,7 +389,7 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
         if (idx >= 0) {
             const Retired R = retire_ray<PATH>(sc, P, G, B, idx, meta, sink.hmin, S.dir, L, aov_prim, aov_inst, aov_t);
             next = R.next; ended = R.ended; no = R.o; nd = R.d; nmeta = R.meta;
-            if (next) B.acc[idx] = make_float4(R.acc.x, R.acc.y, R.acc.z, 0.f);
+            if (next) st_stream(B.acc + idx, make_float4(R.acc.x, R.acc.y, R.acc.z, 0.f));
             if (ended) {                                        // radiance -> 8-bit BGR pixel (PATH: mean over samples)
                 const float scale = PATH ? 1.0f / (float)P.spp : 1.0f;
                 unsigned char* p = img + (size_t)R.y * pitch + 3 * (size_t)R.x;
@@ -417,8 +416,8 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
                 if (!kept) {
                     const unsigned pos = base + __popc(nm & lt), slot = pos & (Q.cap - 1u);
                     const size_t e = (size_t)r0 * Q.cap + slot;
-                    Q.org[e] = make_float4(no.x, no.y, no.z, __int_as_float(idx));
-                    Q.dir[e] = make_float4(nd.x, nd.y, nd.z, __uint_as_float(nmeta));
+                    st_stream(Q.org + e, make_float4(no.x, no.y, no.z, __int_as_float(idx)));
+                    st_stream(Q.dir + e, make_float4(nd.x, nd.y, nd.z, __uint_as_float(nmeta)));
                     __threadfence();
                     *(volatile unsigned*)(Q.ticket + e) = pos + 1u;
                 } else {
@@ -471,7 +470,7 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
                     unsigned wait = 0;
                     while (ld_volatile_u32(Q.ticket + e) != pos + 1u) { if (++wait > (1u << 26)) { ctr->overflow = 1; break; } }
                     __threadfence();
-                    const float4 o = __ldcg(Q.org + e), d = __ldcg(Q.dir + e);
+                    const float4 o = ld_stream(Q.org + e), d = ld_stream(Q.dir + e);
                     idx = __float_as_int(o.w); meta = __float_as_uint(d.w);
                     sink.reset(idx, (meta & 1u) != 0u);
                     S.begin(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), stk);
@@ -572,8 +571,11 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
     const int ri = g_tune.refill_idle;
     const int grid = std::min(sms * (count ? 4 : mb), (G.n_slots + 127) / 128);
     const bool smem = sc.top_tlas_n + sc.top_blas_n > 0;
-    const size_t shb = smem ? (size_t)(sc.top_tlas_n + sc.top_blas_n) * 128 + 16 : 0;
-    if (g_tune.fused == 2) {                                            // in-kernel ray queue variant
+    const size_t shb = smem ? (size_t)(sc.top_tlas_n + sc.top_blas_n) * NODE_F4 * 16 + 16 : 0;
+    // The queue variant wins when the frame is long enough to amortise its tail (measured on C3: 4.1 M slots 4.92 vs 5.12 ms,
+    // 2.1 M slots 3.10 vs 2.86 ms) and always for path tracing, whose chains run for spp samples (C4 at 1/8: 9.3 vs 10.3 ms).
+    const int variant = g_tune.fused >= 0 ? g_tune.fused : (path || G.n_slots >= 3000000 ? 2 : 1);
+    if (variant == 2) {                                                 // in-kernel ray queue variant
         size_t qcap = 8192;                                             // entries per ring; a full ring falls back to in-lane tracing
         while (qcap * QR_RINGS < 2 * (size_t)G.n_slots) qcap <<= 1;
         if (m->q_cap < qcap) {
@@ -591,7 +593,7 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
         MCK(cudaMemsetAsync(m->q_ticket, 0, sizeof(unsigned) * m->q_cap * QR_RINGS, st));
         MCK(cudaMemsetAsync(m->q_ctl, 0, sizeof(unsigned) * (QR_RINGS * QR_CTL + 32), st));
         QRing Q;
-        Q.org = m->q_org; Q.dir = m->q_dir; Q.ticket = m->q_ticket; Q.ctl = m->q_ctl; Q.pending = m->q_ctl + QR_RINGS * QR_CTL;
+        Q.org = m->q_org; Q.dir = m->q_dir; Q.ticket = m->q_ticket; Q.ctl = m->q_ctl;
         Q.cap = (unsigned)m->q_cap;
         MegaGeo GQ = G;
         GQ.order = nullptr;                                             // no cost map in this variant

@@ -8,7 +8,8 @@ namespace rtb {
 struct Tune {
     int trace_minb = 8;     // __launch_bounds__(128, N) variant of the queue tracer: resident blocks per SM the registers allow
     int direct_minb = 8;    // same for the direct kernel
-    int fused = 2;          // modes 2/3: 2 = one persistent kernel + in-kernel ray queues (k_megaq), 1 = the same without queues (k_mega), 0 = staged wavefront pipeline
+    int fused = -1;         // modes 2/3: 2 = one persistent kernel + in-kernel ray queues (k_megaq), 1 = the same without queues (k_mega),
+                            // 0 = staged wavefront pipeline, -1 = choose 1 or 2 per frame (launch_mega: queues pay off from ~3 M pixel slots)
     int smem_top = 0;       // BLAS nodes (top levels, BFS prefix) staged in shared memory by TMA bulk copy; 0 = off (measured slower: profiles/r01e_tune_c3_smem_top.log)
     int queue_keep = 28;    // queue variant (fused=2): a warp whose continuing rays number at least this keeps them in their lanes
     int tail_idle = 2;      // fused kernel, after the last pixel was claimed: retire once this many live lanes are idle

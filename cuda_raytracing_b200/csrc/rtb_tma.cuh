@@ -19,12 +19,12 @@ struct TopLevels {                  // CTA-uniform view of what was staged
 
 XF unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 
-// smem: dynamic shared memory, 128-byte aligned, (n_tlas + n_blas) * 128 + 16 bytes; called by every thread of the CTA
+// smem: dynamic shared memory, 128-byte aligned, (n_tlas + n_blas) * NODE_F4 * 16 + 16 bytes; called by every thread of the CTA
 XF void stage_top_levels(const SceneDev& sc, float4* smem, TopLevels& T)
 {
     T.n_tlas = sc.top_tlas_n; T.n_blas = sc.top_blas_n; T.g_blas = sc.top_blas;
     T.s_tlas = smem; T.s_blas = smem + (size_t)T.n_tlas * NODE_F4;
-    const unsigned bytes_t = (unsigned)T.n_tlas * 128u, bytes_b = (unsigned)T.n_blas * 128u;
+    const unsigned bytes_t = (unsigned)T.n_tlas * (NODE_F4 * 16u), bytes_b = (unsigned)T.n_blas * (NODE_F4 * 16u);
     if (bytes_t + bytes_b == 0u) return;
     unsigned long long* mbar = (unsigned long long*)(smem + (size_t)(T.n_tlas + T.n_blas) * NODE_F4);
     const unsigned mb = smem_u32(mbar);

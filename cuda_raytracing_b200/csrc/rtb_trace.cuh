@@ -11,6 +11,7 @@
 #pragma once
 #include "rtb_internal.cuh"
 #include "rtb_tma.cuh"
+#include "rtb_cache.cuh"
 
 namespace rtb {
 
@@ -48,7 +49,7 @@ XF void setup_slabs(InstRay& r)
 // 4 slab tests against one wide node; keys[i] = (bits(tnear) & ~3) | i for hits, 0xffffffff for misses
 // GENERIC: the node may live in shared memory (staged top levels), so plain generic loads instead of ld.global.nc
 template <bool GENERIC>
-XF float4 node_ld(const float4* p) { return GENERIC ? *p : __ldg(p); }
+XF float4 node_ld(const float4* p) { return GENERIC ? *p : ld_keep(p); }
 
 template <bool GENERIC>
 XF void test_node(const float4* __restrict__ node, const InstRay& r, float tmax, unsigned keys[4], int4& refs)
@@ -83,7 +84,7 @@ struct InstXf {                  // instance transform, loaded when a TLAS leaf 
 XF void load_instance(const float4* __restrict__ inst, int i, InstXf& x)
 {
     const float4* p = inst + (size_t)i * INST_F4;
-    float4 a = __ldg(p + 0), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3), e = __ldg(p + 4), f = __ldg(p + 5);
+    float4 a = ld_keep(p + 0), b = ld_keep(p + 1), c = ld_keep(p + 2), d = ld_keep(p + 3), e = ld_keep(p + 4), f = ld_keep(p + 5);
     x.q_pose = a;
     x.pose_t = mk3(b.x, b.y, b.z); x.mesh = __float_as_int(b.w);
     x.inv_scale = mk3(c.x, c.y, c.z); x.material = __float_as_int(c.w);

@@ -178,7 +178,7 @@ struct TraceState {
         while (t0 < t1) {
             const int slot = t0;
             const float4* q = tris + (size_t)slot * TRI_F4;
-            const float4 q0 = __ldg(q + 0), q1 = __ldg(q + 1);
+            const float4 q0 = ld_keep(q + 0), q1 = ld_keep(q + 1);
             if (++t0 == t1) { t0 = u0; t1 = u1; u0 = u1 = 0; }
             if (COUNT) n_tris++;
             const f3 n = mk3(q0.x, q0.y, q0.z);
@@ -191,7 +191,7 @@ struct TraceState {
             if (t < 0.0f) continue;                                           // :72
             const f3 p = xadd(r.o, xscale(r.d, t));                           // :76
             if (p.x == FLT_MAX) continue;                                     // raycast.cu:91
-            const float4 q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+            const float4 q2 = ld_keep(q + 2), q3 = ld_keep(q + 3);
             const f3 e0 = mk3(q2.x, q2.y, q2.z), e1 = mk3(q3.x, q3.y, q3.z);
             const f3 v2 = xsub(p, A);                                         // TrianglePrimitive.hpp:154-156
             const float dot00 = q1.w, dot01 = q2.w, dot11 = q3.w;
@@ -202,7 +202,7 @@ struct TraceState {
             if (!((u >= 0.0f) && (v >= 0.0f) && (xa(u, v) <= 1.0f))) continue;          // :169
             // raycast.cu:98-104 world location through inv_pose, Euclidean distance to the WORLD origin
             const float4* ip = sc.inst + (size_t)cur_inst * INST_F4;
-            const float4 q_inv = __ldg(ip + 3), it = __ldg(ip + 4), sc4 = __ldg(ip + 5);
+            const float4 q_inv = ld_keep(ip + 3), it = ld_keep(ip + 4), sc4 = ld_keep(ip + 5);
             f3 loc = xmul3(p, mk3(sc4.x, sc4.y, sc4.z));
             loc = xapply_quat(q_inv, xsub(loc, mk3(it.x, it.y, it.z)));
             const float distance = xmagnitude(xsub(loc, org));
