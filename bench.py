@@ -220,6 +220,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--exchange", default="direct", choices=["direct", "push", "nccl"],
+                    help="N>1: how the bands reach rank 0 (tiles.PeerFrame direct stores / peer copy, or the NCCL gather)")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
     rank = int(os.environ.get("RANK", "0"))
@@ -260,9 +262,14 @@ def main():
     cam.mode, cam.max_depth, cam.spp = cfg["mode"], cfg["depth"], cfg["spp"]
     cam.tile_rank, cam.tile_count = rank, world
     pitch = W * 3
-    frame = torch.zeros((H, pitch), dtype=torch.uint8, device=dev)
     from cuda_raytracing_b200 import tiles
-    fg = tiles.FrameGather(H, pitch, rank, world, dev)
+    if world > 1 and args.exchange != "nccl":
+        # frame exchange over NVLink peer memory: ranks > 0 write their bands into rank 0's frame (tiles.PeerFrame)
+        fg = tiles.PeerFrame(scene, H, pitch, rank, world, dev, mode=args.exchange)
+        frame, target = fg.frame, fg.target
+    else:
+        frame = torch.zeros((H, pitch), dtype=torch.uint8, device=dev)
+        fg, target = tiles.FrameGather(H, pitch, rank, world, dev), frame.data_ptr()
     stream = torch.cuda.current_stream()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     host_frame = torch.empty((H, pitch), dtype=torch.uint8).pin_memory()
@@ -273,8 +280,11 @@ def main():
             # animated mesh: new vertex positions arrive in HBM, BLAS is rebuilt on the device
             scene.rebuild_mesh(0, device_ptr=anim[i % len(anim)].data_ptr(), n=len(tris))
         cam.pose = np.array(camera_pose(cfg, i), np.float32)
-        cam.render_scene(scene, frame.data_ptr(), pitch, stream=C.c_void_p(stream.cuda_stream))
-        fg.gather(frame)
+        cam.render_scene(scene, target, pitch, stream=C.c_void_p(stream.cuda_stream))
+        if isinstance(fg, tiles.PeerFrame):
+            fg.gather(stream.cuda_stream)
+        else:
+            fg.gather(frame)
         if e2e and rank == 0:
             host_frame.copy_(frame, non_blocking=True)
             stream.synchronize()
@@ -402,7 +412,9 @@ def main():
                     ms_per_step=ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
                     config=dict(workload=cfg["desc"], config=args.config, width=W, height=H, triangles=int(len(tris)),
                                 instances=len(scene_instances(cfg)), mode=cfg["mode"], max_depth=cfg["depth"], spp=cfg["spp"],
-                                parallelism="image bands of %d rows interleaved over %d GPU(s), scene replicated, NCCL gather to rank 0" % (api.BAND_ROWS, world),
+                                parallelism="image bands of %d rows interleaved over %d GPU(s), scene replicated, bands to rank 0: %s" % (
+                                    api.BAND_ROWS, world, {"direct": "kernel stores into rank 0's frame over NVLink peer memory",
+                                                           "push": "one strided peer copy per rank over NVLink", "nccl": "NCCL gather"}[args.exchange] if world > 1 else "-"),
                                 l2="flushed between steps with a 256 MiB write (untimed)" if not args.no_flush else "not flushed",
                                 rays_per_frame=rays / args.steps, blas=dict(nodes=info["num_nodes"], leaves=info["num_leaves"], depth=info["depth"],
                                                                          build_ms=info["build_ms"], bytes=info["device_bytes"])),
@@ -414,6 +426,10 @@ def main():
             line["ref_cuda"] = ref_cuda
         print(json.dumps(line), flush=True)
     if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()                                   # nobody unmaps / frees the shared frame while a peer may still write
+        if isinstance(fg, tiles.PeerFrame):
+            fg.close()
         dist.destroy_process_group()
     scene.close()
 

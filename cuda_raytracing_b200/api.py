@@ -62,7 +62,8 @@ EXPORTS = ["rtb_context_create", "rtb_context_destroy", "rtb_last_error", "rtb_v
            "rtb_mesh_create", "rtb_mesh_rebuild", "rtb_mesh_info_get", "rtb_mesh_read", "rtb_mesh_destroy", "rtb_texture_upload",
            "rtb_set_materials", "rtb_set_instances", "rtb_update_instance", "rtb_render", "rtb_render_host",
            "rtb_synchronize", "rtb_frame_stats_get", "rtb_debug_math", "rtb_invert_intrinsic", "rtb_invert_lre",
-           "rtb_instance_build_inv", "rtb_triangle_init", "rtb_obj_load", "rtb_free"]
+           "rtb_instance_build_inv", "rtb_triangle_init", "rtb_obj_load", "rtb_free",
+           "rtb_frame_alloc_shared", "rtb_frame_free_shared", "rtb_frame_open_shared", "rtb_frame_close_shared", "rtb_push_bands"]
 
 _lib = None
 
@@ -110,6 +111,11 @@ def lib():
     L.rtb_triangle_init.restype = None
     L.rtb_obj_load.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(ci)]
     L.rtb_free.argtypes = [vp]
+    L.rtb_frame_alloc_shared.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]
+    L.rtb_frame_free_shared.argtypes = [vp, vp]
+    L.rtb_frame_open_shared.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    L.rtb_frame_close_shared.argtypes = [vp, vp]
+    L.rtb_push_bands.argtypes = [vp, vp, vp, C.c_size_t, ci, ci, ci, vp]
     L.rtb_free.restype = None
     _lib = L
     return L
@@ -288,6 +294,27 @@ class Scene:
         out = np.zeros_like(x)
         _check(lib().rtb_debug_math(self._ctx, what, x.ctypes.data, out.ctypes.data, x.size))
         return out
+
+    # ---- multi-GPU frame exchange over peer memory (rtb200.h: rtb_frame_*_shared, rtb_push_bands) ----
+    def shared_alloc(self, nbytes):
+        """-> (device pointer, 64-byte IPC handle) of a frame other processes on this node can map."""
+        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+        _check(lib().rtb_frame_alloc_shared(self._ctx, nbytes, C.byref(ptr), handle))
+        return ptr.value, handle.raw
+
+    def shared_free(self, ptr):
+        _check(lib().rtb_frame_free_shared(self._ctx, ptr))
+
+    def shared_open(self, handle):
+        ptr = C.c_void_p()
+        _check(lib().rtb_frame_open_shared(self._ctx, C.create_string_buffer(bytes(handle), 64), C.byref(ptr)))
+        return ptr.value
+
+    def shared_close(self, ptr):
+        _check(lib().rtb_frame_close_shared(self._ctx, ptr))
+
+    def push_bands(self, src_ptr, dst_ptr, pitch, height, rank, world, stream=None):
+        _check(lib().rtb_push_bands(self._ctx, src_ptr, dst_ptr, pitch, height, rank, world, stream))
 
     def frame_stats(self):
         st = FrameStats()

@@ -500,6 +500,72 @@ int rtb_render_host(rtb_context* c, const rtb_render_params* p, unsigned char* i
     return RTB_OK;
 }
 
+// ------------------------------------------------------------------ multi-GPU frame exchange over peer memory
+int rtb_frame_alloc_shared(rtb_context* c, size_t bytes, unsigned char** dev, unsigned char handle[RTB_IPC_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == RTB_IPC_HANDLE_BYTES, "handle size");
+    if (!c || !dev || !handle || !bytes) return fail(RTB_ERR_INVALID, "rtb_frame_alloc_shared: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    void* p = nullptr;
+    CU(cudaMalloc(&p, bytes), "cudaMalloc shared frame");
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); return fail(RTB_ERR_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e)); }
+    CU(cudaMemset(p, 0, bytes), "cudaMemset shared frame");
+    memcpy(handle, &h, sizeof h);
+    *dev = (unsigned char*)p;
+    return RTB_OK;
+}
+
+int rtb_frame_free_shared(rtb_context* c, unsigned char* dev)
+{
+    if (!c) return fail(RTB_ERR_INVALID, "rtb_frame_free_shared: NULL context");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    if (dev) CU(cudaFree(dev), "cudaFree shared frame");
+    return RTB_OK;
+}
+
+int rtb_frame_open_shared(rtb_context* c, const unsigned char handle[RTB_IPC_HANDLE_BYTES], unsigned char** dev)
+{
+    if (!c || !dev || !handle) return fail(RTB_ERR_INVALID, "rtb_frame_open_shared: NULL argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    void* p = nullptr;
+    CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle");
+    *dev = (unsigned char*)p;
+    return RTB_OK;
+}
+
+int rtb_frame_close_shared(rtb_context* c, unsigned char* dev)
+{
+    if (!c) return fail(RTB_ERR_INVALID, "rtb_frame_close_shared: NULL context");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    if (dev) CU(cudaIpcCloseMemHandle(dev), "cudaIpcCloseMemHandle");
+    return RTB_OK;
+}
+
+int rtb_push_bands(rtb_context* c, const unsigned char* src, unsigned char* dst, size_t pitch, int height, int tile_rank, int tile_count, void* stream)
+{
+    if (!c || !src || !dst || !pitch || height <= 0 || tile_count <= 0 || tile_rank < 0 || tile_rank >= tile_count)
+        return fail(RTB_ERR_INVALID, "rtb_push_bands: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int bands = (height + rtb::BAND_ROWS - 1) / rtb::BAND_ROWS;
+    const int mine = (bands - tile_rank + tile_count - 1) / tile_count;            // bands tile_rank, tile_rank + tile_count, ...
+    if (mine <= 0) return RTB_OK;
+    const int last = tile_rank + (mine - 1) * tile_count;                           // my last band: may be cut by the frame's end
+    const int last_rows = std::min(rtb::BAND_ROWS, height - last * rtb::BAND_ROWS);
+    const int full = last_rows == rtb::BAND_ROWS ? mine : mine - 1;
+    const size_t band_bytes = (size_t)rtb::BAND_ROWS * pitch, stride = band_bytes * (size_t)tile_count, off = band_bytes * (size_t)tile_rank;
+    if (full > 0) CU(cudaMemcpy2DAsync(dst + off, stride, src + off, stride, band_bytes, (size_t)full, cudaMemcpyDefault, st), "band push");
+    if (full < mine) {
+        const size_t o = band_bytes * (size_t)last;
+        CU(cudaMemcpyAsync(dst + o, src + o, (size_t)last_rows * pitch, cudaMemcpyDefault, st), "band push (last band)");
+    }
+    return RTB_OK;
+}
+
 int rtb_synchronize(rtb_context* c)
 {
     if (!c) return fail(RTB_ERR_INVALID, "rtb_synchronize: NULL context");

@@ -62,3 +62,61 @@ class FrameGather:
             req.wait()
         frame.index_copy_(0, self.dst_rows, self.recv.view(-1, self.pitch).index_select(0, self.src_idx))
         return frame
+
+
+class _DevicePointer:
+    """Minimal __cuda_array_interface__ carrier: lets torch view memory this package allocated (rtb_frame_alloc_shared)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False), "version": 3, "strides": None}
+
+
+class PeerFrame:
+    """The per-frame exchange over NVLink peer memory instead of a collective (one process per GPU, one NVSwitch node).
+
+    Rank 0 owns the complete frame in memory allocated by the library (`Scene.shared_alloc`) and broadcasts its CUDA IPC
+    handle once; every other rank maps it.  Per frame a rank r > 0 either
+      * mode "direct": renders its bands straight into the mapped frame -- the kernels' pixel stores are the transfer,
+        nothing is packed, copied or unpacked afterwards; or
+      * mode "push":   renders into a local frame and enqueues ONE strided peer copy of the bands it owns
+        (`rtb_push_bands`, a cudaMemcpy2DAsync over NVLink) behind the render kernel.
+    A 4-byte all-reduce on the same stream then tells rank 0 that every band has landed (stream ordered: no host sync).
+    `target` is the device pointer this rank passes to `Camera.render_scene`; `frame` (rank 0) is the complete image."""
+
+    def __init__(self, scene, height, pitch, rank, world, device, mode="direct", group=None):
+        assert mode in ("direct", "push")
+        self.scene, self.h, self.pitch, self.rank, self.world, self.mode, self.group = scene, height, pitch, rank, world, mode, group
+        self.shared = self.peer = None
+        self.flag = torch.zeros(1, dtype=torch.int32, device=device)
+        box = [None]
+        if rank == 0:
+            self.shared, handle = scene.shared_alloc(height * pitch)
+            box[0] = handle
+        if world > 1:
+            dist.broadcast_object_list(box, src=0, group=group)
+        if rank == 0:
+            self.frame = torch.as_tensor(_DevicePointer(self.shared, (height, pitch)), device=device)
+            self.target = self.shared
+        else:
+            self.peer = scene.shared_open(box[0])
+            self.frame = torch.zeros((height, pitch), dtype=torch.uint8, device=device) if mode == "push" else None
+            self.target = self.frame.data_ptr() if mode == "push" else self.peer
+
+    def gather(self, stream=None):
+        """Call after this rank's render was enqueued on `stream` (a cudaStream_t value or None for the current torch stream)."""
+        if self.world == 1:
+            return self.frame
+        if self.rank != 0 and self.mode == "push":
+            s = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+            self.scene.push_bands(self.frame.data_ptr(), self.peer, self.pitch, self.h, self.rank, self.world, s)
+        dist.all_reduce(self.flag, group=self.group)
+        return self.frame
+
+    def close(self):
+        if self.peer:
+            self.scene.shared_close(self.peer)
+            self.peer = None
+        if self.shared:
+            self.frame = None
+            self.scene.shared_free(self.shared)
+            self.shared = None

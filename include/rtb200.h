@@ -129,6 +129,21 @@ RTB_API int rtb_render_host(rtb_context* ctx, const rtb_render_params* p, unsign
                             const rtb_aovs* aovs_host);
 RTB_API int rtb_synchronize(rtb_context* ctx);                                            /* cudaDeviceSynchronize, kernel.cu:279 */
 RTB_API int rtb_frame_stats_get(rtb_context* ctx, rtb_frame_stats* out);
+/* ---- multi-GPU frame exchange over peer memory (one process per GPU on one NVSwitch node; no counterpart in the
+ *      reference, which renders on one GPU -- this is the (e) row of SURVEY.md 8).  The rank that owns the complete
+ *      frame allocates it with rtb_frame_alloc_shared and passes the 64-byte handle to the other processes (any
+ *      channel: torch.distributed object broadcast in tiles.py); they map it with rtb_frame_open_shared and either
+ *      render their bands straight into the mapped pointer (rtb_render: the pixel stores travel over NVLink) or
+ *      render locally and enqueue rtb_push_bands (one strided peer copy of the bands they own).  Both are stream
+ *      ordered; the caller signals completion to the owner (a 4-byte all-reduce in tiles.py). */
+#define RTB_IPC_HANDLE_BYTES 64
+RTB_API int rtb_frame_alloc_shared(rtb_context* ctx, size_t bytes, unsigned char** dev_ptr, unsigned char handle[RTB_IPC_HANDLE_BYTES]);
+RTB_API int rtb_frame_free_shared(rtb_context* ctx, unsigned char* dev_ptr);
+RTB_API int rtb_frame_open_shared(rtb_context* ctx, const unsigned char handle[RTB_IPC_HANDLE_BYTES], unsigned char** dev_ptr);
+RTB_API int rtb_frame_close_shared(rtb_context* ctx, unsigned char* dev_ptr);
+/* copies rows [8b, 8b+8) for every band b with b % tile_count == tile_rank from src to dst (same pitch and height) */
+RTB_API int rtb_push_bands(rtb_context* ctx, const unsigned char* src, unsigned char* dst, size_t pitch, int height,
+                           int tile_rank, int tile_count, void* stream);
 /* Evaluates a device math helper on n host floats (tests): what = 0 atanf with host-libm bits (raycast.cu:170),
  * 1 Q_rsqrt (utils.hpp:12-27). */
 RTB_API int rtb_debug_math(rtb_context* ctx, int what, const float* in_host, float* out_host, int n);
