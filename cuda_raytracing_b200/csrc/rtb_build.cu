@@ -39,6 +39,7 @@ struct BuildCounters {
     int n_leaves, max_leaf, max_level;
     float sah;
     int qcount[72];         // collapse work-queue sizes per level
+    unsigned bar;           // grid barrier of the collapse kernel
 };
 
 // ------------------------------------------------------------------ 1. primitive boxes
@@ -59,6 +60,7 @@ __global__ void k_init_counters(BuildCounters* c)
     if (t < 3) { c->bounds[t] = f2ord(FLT_MAX); c->bounds[t + 3] = f2ord(-FLT_MAX); c->cbounds[t] = f2ord(FLT_MAX); c->cbounds[t + 3] = f2ord(-FLT_MAX); }
     if (t == 0) { c->n_wide = 1; c->n_leaves = 0; c->max_leaf = 0; c->max_level = 0; c->sah = 0.f; }
     if (t < 72) c->qcount[t] = 0;
+    if (t == 72) c->bar = 0u;
 }
 
 __global__ void __launch_bounds__(256) k_scene_bounds(const float4* __restrict__ bmin, const float4* __restrict__ bmax, int n, BuildCounters* c)
@@ -222,61 +224,105 @@ __device__ __forceinline__ void slot_range(int id, int n, const int2* __restrict
     else { int2 r = range[id]; first = r.x; count = r.y - r.x + 1; }
 }
 
-__global__ void __launch_bounds__(128) k_collapse(int level, const int2* __restrict__ q_in, int2* __restrict__ q_out, int n,
+// ONE persistent launch for the whole collapse (it was one launch per level, 70 of them: the host does not know the depth).
+// Levels are separated by a grid barrier (every CTA is resident: the grid is sized from the occupancy query); a wide
+// node's index is (number of nodes of all earlier levels) + (its position in this level's queue), so one level's nodes --
+// and the children of one node -- are contiguous in memory, and the only atomic is one per warp on the next level's count.
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned target)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1u);
+        while (*(volatile unsigned*)bar < target) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(128) k_collapse(int2* __restrict__ q0, int2* __restrict__ q1, int n,
                                                   const int* __restrict__ left, const int* __restrict__ right,
                                                   const int2* __restrict__ range, const float4* __restrict__ nb_min,
                                                   const float4* __restrict__ nb_max, const unsigned char* __restrict__ flags,
                                                   float4* __restrict__ nodes, BuildCounters* c)
 {
-    const int items = c->qcount[level];
-    int my_leaves = 0, my_maxleaf = 0;
-    for (int it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
-        int2 item = q_in[it];
-        int slot[4]; int ns;
-        if (flags[item.x]) { slot[0] = item.x; ns = 1; }                 // whole tree is one leaf (tiny meshes)
-        else { slot[0] = left[item.x]; slot[1] = right[item.x]; ns = 2; }
-        while (ns < 4) {
-            int best = -1; float barea = -1.f;
-            for (int k = 0; k < ns; k++) {
-                int id = slot[k];
-                if (id < n - 1 && !flags[id]) { float a = nb_min[id].w; if (a > barea) { barea = a; best = k; } }
-            }
-            if (best < 0) break;
-            int id = slot[best];
-            slot[best] = left[id];
-            slot[ns++] = right[id];
-        }
-        float lo[3][4], hi[3][4]; int ref[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            if (k < ns) {
-                int id = slot[k];
-                float4 a = nb_min[id], b = nb_max[id];
-                lo[0][k] = a.x; lo[1][k] = a.y; lo[2][k] = a.z; hi[0][k] = b.x; hi[1][k] = b.y; hi[2][k] = b.z;
-                if (id >= n - 1 || flags[id]) {
-                    int first, count; slot_range(id, n, range, first, count);
-                    ref[k] = ~((first << 3) | (count - 1));
-                    my_leaves++; my_maxleaf = max(my_maxleaf, count);
-                } else {
-                    int w = atomicAdd(&c->n_wide, 1);
-                    int qi = atomicAdd(&c->qcount[level + 1], 1);
-                    q_out[qi] = make_int2(id, w);
-                    ref[k] = w;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    int my_leaves = 0, my_maxleaf = 0, level = 0;
+    int start = 0;                                                      // wide nodes of the levels before the next one
+    for (; level < 70; level++) {
+        const int items = *(volatile int*)&c->qcount[level];
+        if (items == 0) break;
+        start += items;
+        const int2* q_in = (level & 1) ? q1 : q0;
+        int2* q_out = (level & 1) ? q0 : q1;
+        for (int it0 = warp * 32; it0 < items; it0 += n_warps * 32) {
+            const int it = it0 + lane;
+            const bool active = it < items;
+            int2 item = make_int2(0, 0);
+            int slot[4] = { 0, 0, 0, 0 }; int ns = 0;
+            bool inner[4] = { false, false, false, false };
+            int kc = 0;
+            if (active) {
+                item = __ldcg(q_in + it);
+                if (flags[item.x]) { slot[0] = item.x; ns = 1; }             // whole tree is one leaf (tiny meshes)
+                else { slot[0] = left[item.x]; slot[1] = right[item.x]; ns = 2; }
+                while (ns < 4) {
+                    int best = -1; float barea = -1.f;
+                    for (int k = 0; k < ns; k++) {
+                        int id = slot[k];
+                        if (id < n - 1 && !flags[id]) { float a = nb_min[id].w; if (a > barea) { barea = a; best = k; } }
+                    }
+                    if (best < 0) break;
+                    int id = slot[best];
+                    slot[best] = left[id];
+                    slot[ns++] = right[id];
                 }
-            } else {
-                // empty slot: lo = hi = +inf can never pass a slab test (an inverted box would: min/max un-invert it)
-                lo[0][k] = lo[1][k] = lo[2][k] = __int_as_float(0x7f800000);
-                hi[0][k] = hi[1][k] = hi[2][k] = __int_as_float(0x7f800000);
-                ref[k] = EMPTY_REF;
+#pragma unroll
+                for (int k = 0; k < 4; k++) { inner[k] = k < ns && slot[k] < n - 1 && !flags[slot[k]]; kc += inner[k] ? 1 : 0; }
             }
+            // next level's queue positions for this warp's interior children: exclusive scan + one atomic
+            int pre = kc;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += v; }
+            const int total = __shfl_sync(0xffffffffu, pre, 31);
+            int base = 0;
+            if (lane == 0 && total) base = atomicAdd(&c->qcount[level + 1], total);
+            base = __shfl_sync(0xffffffffu, base, 0) + pre - kc;
+            if (!active) continue;
+            float lo[3][4], hi[3][4]; int ref[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                if (k < ns) {
+                    int id = slot[k];
+                    float4 a = nb_min[id], b = nb_max[id];
+                    lo[0][k] = a.x; lo[1][k] = a.y; lo[2][k] = a.z; hi[0][k] = b.x; hi[1][k] = b.y; hi[2][k] = b.z;
+                    if (!inner[k]) {
+                        int first, count; slot_range(id, n, range, first, count);
+                        ref[k] = ~((first << 3) | (count - 1));
+                        my_leaves++; my_maxleaf = max(my_maxleaf, count);
+                    } else {
+                        const int qi = base++;
+                        q_out[qi] = make_int2(id, start + qi);
+                        ref[k] = start + qi;
+                    }
+                } else {
+                    // empty slot: lo = hi = +inf can never pass a slab test (an inverted box would: min/max un-invert it)
+                    lo[0][k] = lo[1][k] = lo[2][k] = __int_as_float(0x7f800000);
+                    hi[0][k] = hi[1][k] = hi[2][k] = __int_as_float(0x7f800000);
+                    ref[k] = EMPTY_REF;
+                }
+            }
+            float4* nd = nodes + (size_t)item.y * NODE_F4;
+            nd[0] = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd[1] = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+            nd[2] = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]); nd[3] = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
+            nd[4] = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd[5] = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+            nd[6] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), __int_as_float(ref[2]), __int_as_float(ref[3]));
         }
-        float4* nd = nodes + (size_t)item.y * NODE_F4;
-        nd[0] = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd[1] = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
-        nd[2] = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]); nd[3] = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
-        nd[4] = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd[5] = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
-        nd[6] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), __int_as_float(ref[2]), __int_as_float(ref[3]));
+        grid_barrier(&c->bar, (unsigned)gridDim.x * (unsigned)(level + 1));
     }
-    if (my_leaves) { atomicAdd(&c->n_leaves, my_leaves); atomicMax(&c->max_leaf, my_maxleaf); atomicMax(&c->max_level, level); }
+    if (my_leaves) { atomicAdd(&c->n_leaves, my_leaves); atomicMax(&c->max_leaf, my_maxleaf); }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { c->max_level = level - 1; c->n_wide = start; }
 }
 
 // n == 0 / n == 1 trees: a root with no child / one single-primitive leaf
@@ -361,15 +407,15 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     CK(cudaMemcpyAsync(q0, &root_item, sizeof(int2), cudaMemcpyHostToDevice, st));
     int one = 1;
     CK(cudaMemcpyAsync(&ctr->qcount[0], &one, sizeof(int), cudaMemcpyHostToDevice, st));
-    long long width = 1;
-    for (int level = 0; level < 70; level++) {
-        long long items = width < (long long)n ? width : (long long)n;
-        int grid = (int)((items + 127) / 128);
-        if (grid > 148 * 16) grid = 148 * 16;
-        k_collapse<<<grid, 128, 0, st>>>(level, (level & 1) ? q1 : q0, (level & 1) ? q0 : q1, n, left, right, range, nb_min, nb_max,
-                                         flags, out.nodes, ctr);
-        if (width < (long long)n) width *= 4;
+    static int resident = 0;                                            // CTAs of k_collapse that fit the device at once
+    if (!resident) {
+        int dev = 0, sms = 0, per_sm = 0;
+        CK(cudaGetDevice(&dev));
+        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_collapse, 128, 0));
+        resident = sms * std::max(1, std::min(per_sm, 8));
     }
+    k_collapse<<<std::min(resident, (n + 127) / 128), 128, 0, st>>>(q0, q1, n, left, right, range, nb_min, nb_max, flags, out.nodes, ctr);
     return cudaGetLastError();
 }
 
