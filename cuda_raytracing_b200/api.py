@@ -168,7 +168,8 @@ class OBJLoader:
         rc = lib().rtb_obj_load(path.encode(), C.byref(p), C.byref(n))
         if rc != 0:
             raise RtbError("Could not open file %s" % path)
-        tris = np.frombuffer(C.string_at(p.value, n.value * 72), dtype=TRI).copy() if n.value else np.zeros(0, TRI)
+        # one copy out of the loader's malloc'ed array (freed right below)
+        tris = np.frombuffer((C.c_ubyte * (n.value * 72)).from_address(p.value), dtype=TRI).copy() if n.value else np.zeros(0, TRI)
         lib().rtb_free(p)
         return MeshPrimitive(tris)
 

@@ -159,6 +159,57 @@ def test_obj_loader_vs_reference(oracle, refhost, tmp_path):
     assert a["uv"][has_uv].tobytes() == r["uv"][has_uv].tobytes()
 
 
+def test_obj_loader_number_spellings_and_large_file(oracle, refhost, rtb, tmp_path):
+    """The product loader parses numbers with its own exact fast path and cuts the file into one chunk per host thread:
+    every spelling must give strtof's bits, and a file large enough to be cut (> 256 KB per chunk) the same triangles
+    as the oracle's and the reference's sequential loaders."""
+    rng = np.random.default_rng(5)
+    spell = ["0", "-0", "+1", "1.", ".5", "-.25", "+.125e1", "1e-3", "1E3", "123456789", "0.000001", "3.4028234e38", "1e-22", "1e22",
+             "16777217", "0.1", "0.2", "0.3", "1.17549435e-38", "7.0064923e-46", "9007199254740993", "1.00000005960464477539062500",
+             "1.00000017881393432617187500", "0.5000000298023223876953125", "12345678901234567890.5", "1e23", "1e-23", "4.35e-8"]
+    nums = list(spell)
+    for _ in range(6000):
+        k = rng.integers(0, 4)
+        if k == 0: nums.append("%.6f" % rng.uniform(-100, 100))
+        elif k == 1: nums.append("%.9g" % rng.uniform(-1e-3, 1e-3))
+        elif k == 2: nums.append("%.17g" % rng.standard_normal())
+        else: nums.append("%de%d" % (rng.integers(-99999, 99999), rng.integers(-25, 25)))
+    while len(nums) % 3: nums.append("1")
+    p = str(tmp_path / "spell.obj")
+    nv = len(nums) // 3
+    with open(p, "w") as fh:
+        fh.write("# numbers\r\n\n   \n")
+        for i in range(nv):
+            fh.write("%sv %s\t%s %s%s" % ("  " if i % 7 == 0 else "", nums[3 * i], nums[3 * i + 1], nums[3 * i + 2], "\r\n" if i % 5 == 0 else "\n"))
+        for i in range(0, nv - 2, 3):
+            fh.write("f %d %d %d\n" % (i + 1, i + 2, i + 3))
+        fh.write("f 1 2 3 4")                                    # no newline at the end of the file
+    a = oracle.obj_load(p)
+    b = rtb.OBJLoader.load(p).triangles
+    assert len(a) == len(b) and a["v"].tobytes() == b["v"].tobytes() and a["n"].tobytes() == b["n"].tobytes()
+    # large file: > 20 chunks worth of text, mixed token forms, compared with both sequential loaders
+    verts, faces = synth.bumpy_sphere_mesh(150, 300)[:2]
+    vts = rng.random((len(verts), 2)).astype(np.float32)
+    big = str(tmp_path / "big.obj")
+    synth.write_obj(big, verts, faces, vts, faces)
+    assert os.path.getsize(big) > 4 << 20
+    a = oracle.obj_load(big)
+    b = rtb.OBJLoader.load(big).triangles
+    r = refhost.mesh_triangles(refhost.obj_load(big))
+    assert len(a) == len(b) == len(r) == len(faces)
+    for k in ("v", "n", "uv"):
+        assert a[k].tobytes() == b[k].tobytes() == r[k].tobytes(), k
+    # an index that names no vertex fails loudly (the reference reads out of bounds); `v//vn` corners carry no uv
+    bad = str(tmp_path / "bad.obj")
+    open(bad, "w").write("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 7\n")
+    with pytest.raises(Exception):
+        rtb.OBJLoader.load(bad)
+    vn = str(tmp_path / "vn.obj")
+    open(vn, "w").write("v 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nf 1//1 2//1 3//1\n")
+    t = rtb.OBJLoader.load(vn).triangles
+    assert len(t) == 1 and not t["uv"].any() and np.allclose(t["n"][0], (0, 0, 1), atol=2e-3)
+
+
 # ------------------------------------------------------------------ product host math (kernel inputs) vs oracle
 def test_product_host_math_bit_exact(oracle, rtb):
     rng = np.random.default_rng(11)
