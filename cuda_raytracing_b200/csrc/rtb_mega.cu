@@ -550,13 +550,17 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
         MCK(cudaMalloc((void**)&m->order, sizeof(int) * (size_t)G.nb));
         m->cap = (size_t)G.n_slots; m->nb_cap = G.nb;
     }
-    const bool have_hist = g_tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
+    // The queue variant wins when the frame is long enough to amortise its tail (measured on C3: 4.1 M slots 4.92 vs 5.12 ms,
+    // 2.1 M slots 3.10 vs 2.86 ms) and always for path tracing, whose chains run for spp samples (C4 at 1/8: 9.3 vs 10.3 ms).
+    const int variant = g_tune.fused >= 0 ? g_tune.fused : (path || G.n_slots >= 3000000 ? 2 : 1);
+    const bool have_hist = variant == 1 && g_tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
                            m->hist_count == P.tile_count && m->hist_mode == P.mode;
     if (have_hist) { k_order<<<1, 1024, 0, st>>>(m->cost, G.nb, m->order); g_wave_launches_pre = 1; }
     else { MCK(cudaMemsetAsync(m->cost, 0, sizeof(unsigned) * (size_t)G.nb, st)); g_wave_launches_pre = 0; }
     G.order = have_hist ? m->order : nullptr;
     G.cost = m->cost;
-    m->hist_w = P.width; m->hist_h = P.height; m->hist_rank = P.tile_rank; m->hist_count = P.tile_count; m->hist_mode = P.mode;
+    m->hist_w = variant == 1 ? P.width : 0;                              // the queue variant keeps no cost map
+    m->hist_h = P.height; m->hist_rank = P.tile_rank; m->hist_count = P.tile_count; m->hist_mode = P.mode;
     MCK(cudaMemsetAsync(m->head, 0, sizeof(int), st));
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -572,9 +576,6 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
     const int grid = std::min(sms * (count ? 4 : mb), (G.n_slots + 127) / 128);
     const bool smem = sc.top_tlas_n + sc.top_blas_n > 0;
     const size_t shb = smem ? (size_t)(sc.top_tlas_n + sc.top_blas_n) * NODE_F4 * 16 + 16 : 0;
-    // The queue variant wins when the frame is long enough to amortise its tail (measured on C3: 4.1 M slots 4.92 vs 5.12 ms,
-    // 2.1 M slots 3.10 vs 2.86 ms) and always for path tracing, whose chains run for spp samples (C4 at 1/8: 9.3 vs 10.3 ms).
-    const int variant = g_tune.fused >= 0 ? g_tune.fused : (path || G.n_slots >= 3000000 ? 2 : 1);
     if (variant == 2) {                                                 // in-kernel ray queue variant
         size_t qcap = 8192;                                             // entries per ring; a full ring falls back to in-lane tracing
         while (qcap * QR_RINGS < 2 * (size_t)G.n_slots) qcap <<= 1;
