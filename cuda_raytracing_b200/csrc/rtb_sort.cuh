@@ -4,7 +4,8 @@
 // digit-major histogram table, (3) stable scatter.  The scatter ranks keys inside a tile with
 // warp-synchronous __match_any_sync multi-split: each warp owns 32*KPT consecutive keys, ranks them
 // round by round against per-warp digit counters in shared memory, then the 256 digit columns are
-// prefix-summed across the tile's warps.  HBM-bound streaming work: 2 key reads + 1 pair read/write per pass.
+// prefix-summed across the tile's warps; the tile is then put in digit order in shared memory and written out as runs.
+// HBM-bound streaming work: 2 key reads + 1 pair read/write per pass.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -58,29 +59,36 @@ __global__ void __launch_bounds__(256) rs_scan_rows(unsigned* __restrict__ data,
     if (t == 255) totals[blockIdx.x] = part[255];
 }
 
+// The tile is first sorted by digit INSIDE shared memory (rank -> local position), then written out in local order, so
+// consecutive threads store consecutive addresses of one digit's run (16 keys on average) instead of 32 lanes hitting 32
+// different bins with 8-byte stores (the first version: 1.2 TB/s of DRAM traffic, 195 us per pass on 10 M 64-bit keys).
 template <typename K>
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter(const K* __restrict__ keys_in, const unsigned* __restrict__ vals_in,
+__global__ void __launch_bounds__(RS_THREADS, 3) rs_scatter(const K* __restrict__ keys_in, const unsigned* __restrict__ vals_in,
                                                          K* __restrict__ keys_out, unsigned* __restrict__ vals_out, int n,
                                                          int shift, int nblocks, const unsigned* __restrict__ offs,
                                                          const unsigned* __restrict__ totals)
 {
     __shared__ unsigned cnt[RS_WARPS][256];
-    __shared__ unsigned dbase[256];                 // exclusive prefix of the 256 digit totals
+    __shared__ unsigned dbase[256];                 // exclusive prefix of the 256 digit totals, then (global base - local base) per digit
+    __shared__ K buf[RS_TILE];                      // the tile in digit order: keys, then (re-used) values
+    __shared__ unsigned char dig[RS_TILE];          // digit of the element at each local position
+    __shared__ unsigned wsum[RS_WARPS];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&cnt[0][0])[i] = 0;
-    __syncthreads();
     {   // thread d: exclusive prefix of totals[0..d): warp scan + warp sums (RS_THREADS == 256 digits)
         const unsigned v = totals[threadIdx.x];
         unsigned inc = v;
         for (int o = 1; o < 32; o <<= 1) { unsigned u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
-        if (lane == 31) dbase[w] = inc;             // reuse dbase[0..7] as warp sums for a moment
+        if (lane == 31) wsum[w] = inc;
         __syncthreads();
-        unsigned wsum = 0;
-        for (int ww = 0; ww < w; ww++) wsum += dbase[ww];
-        __syncthreads();
-        dbase[threadIdx.x] = wsum + inc - v;
+        unsigned ws = 0;
+        for (int ww = 0; ww < w; ww++) ws += wsum[ww];
+        dbase[threadIdx.x] = ws + inc - v;
     }
-    const int wbase = blockIdx.x * RS_TILE + w * (32 * RS_KPT);
+    __syncthreads();
+    const int tbase = blockIdx.x * RS_TILE;
+    const int tile_n = min(RS_TILE, n - tbase);
+    const int wbase = tbase + w * (32 * RS_KPT);
     K key[RS_KPT];
     unsigned short off[RS_KPT];
     const unsigned lt = (1u << lane) - 1u;
@@ -102,11 +110,23 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const K* __restrict__ k
         __syncwarp();
     }
     __syncthreads();
-    {   // digit column prefix across warps, seeded with this tile's global offset
+    {   // digit d (= thread d): its count in the tile, the tile-local exclusive prefix over digits, the per-warp local bases
         const int d = threadIdx.x;
-        unsigned run = offs[(size_t)d * nblocks + blockIdx.x] + dbase[d];
+        unsigned tot = 0;
+#pragma unroll
+        for (int ww = 0; ww < RS_WARPS; ww++) tot += cnt[ww][d];
+        unsigned inc = tot;
+        for (int o = 1; o < 32; o <<= 1) { unsigned u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+        __syncthreads();                            // wsum is free again (every thread read it above)
+        if (lane == 31) wsum[w] = inc;
+        __syncthreads();
+        unsigned ws = 0;
+        for (int ww = 0; ww < w; ww++) ws += wsum[ww];
+        const unsigned local = ws + inc - tot;      // first local position of digit d
+        unsigned run = local;
 #pragma unroll
         for (int ww = 0; ww < RS_WARPS; ww++) { unsigned c = cnt[ww][d]; cnt[ww][d] = run; run += c; }
+        dbase[d] = offs[(size_t)d * nblocks + blockIdx.x] + dbase[d] - local;      // global position = dbase[d] + local position
     }
     __syncthreads();
 #pragma unroll
@@ -115,10 +135,22 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const K* __restrict__ k
         if (i < n) {
             unsigned d = (unsigned)(key[r] >> shift) & 255u;
             unsigned pos = cnt[w][d] + off[r];
-            keys_out[pos] = key[r];
-            vals_out[pos] = vals_in[i];
+            off[r] = (unsigned short)pos;
+            buf[pos] = key[r];
+            dig[pos] = (unsigned char)d;
         }
     }
+    __syncthreads();
+    for (int j = threadIdx.x; j < tile_n; j += RS_THREADS) keys_out[dbase[dig[j]] + j] = buf[j];
+    __syncthreads();
+    unsigned* vbuf = (unsigned*)buf;
+#pragma unroll
+    for (int r = 0; r < RS_KPT; r++) {
+        int i = wbase + r * 32 + lane;
+        if (i < n) vbuf[off[r]] = vals_in[i];
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < tile_n; j += RS_THREADS) vals_out[dbase[dig[j]] + j] = vbuf[j];
 }
 
 // `hist` holds 256 * nblocks + 256 counters.  Sorts `bits` low bits; result ends in (keys[0], vals[0]) or (keys[1], vals[1]); returns which.
