@@ -415,7 +415,11 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_collapse, 128, 0));
         resident = sms * std::max(1, std::min(per_sm, 8));
     }
-    k_collapse<<<std::min(resident, (n + 127) / 128), 128, 0, st>>>(q0, q1, n, left, right, range, nb_min, nb_max, flags, out.nodes, ctr);
+    // cooperative launch: the driver starts the grid only when every CTA can be resident at once, so the grid barrier cannot
+    // deadlock against another persistent kernel (a second context building on another stream, a render in flight)
+    float4* nodes_out = out.nodes;
+    void* args[] = { &q0, &q1, &n, &left, &right, &range, &nb_min, &nb_max, &flags, &nodes_out, &ctr };
+    CK(cudaLaunchCooperativeKernel((const void*)k_collapse, dim3(std::min(resident, (n + 127) / 128)), dim3(128), args, 0, st));
     return cudaGetLastError();
 }
 
