@@ -30,6 +30,12 @@ struct MeshRec {
     int tri_cap = 0;
     BvhResult bvh;
     rtb_mesh_info info{};
+    // what the TLAS knows about this mesh (see mesh_cut / pack_instance)
+    bool dynamic = false;           // rebuilt at least once: its world boxes come from the (slightly inflated) root bounds
+    std::vector<float> cut;         // mesh-space boxes (min xyz, max xyz) that together cover every triangle
+    bool cut_valid = false;         // the cut covers the current geometry
+    int cut_budget = 0;             // box budget the cut was made for
+    int cut_serial = 0;             // bumped whenever the cut changes (instances remember the one they were packed against)
 };
 
 struct rtb_context {
@@ -43,6 +49,10 @@ struct rtb_context {
     bool mesh_table_dirty = true;
     BvhResult tlas;
     float4* ibox_min = nullptr; float4* ibox_max = nullptr; int ibox_cap = 0;
+    std::vector<float4> inst_rec_h, ibox_lo_h, ibox_hi_h;   // packed instance records and world boxes (host copies)
+    std::vector<int> inst_serial;  // cut_serial of the mesh each instance was packed against
+    bool tlas_dirty = false;       // a mesh rebuild outgrew the boxes the TLAS was built from: rebuilt before the next frame
+    int opt_inst_cut = 256;        // mesh-space boxes per static mesh used to bound its instances (1 = the root box)
     Counters* counters_d = nullptr;
     Arena ws;                      // build workspace (grow-only)
     Arena stage;                   // triangle upload staging + prim boxes
@@ -128,6 +138,7 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     if (n == "counters") c->opt_counters = value;
     else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
     else if (n == "key_bits") c->opt_key_bits = value;
+    else if (n == "inst_cut") { c->opt_inst_cut = std::max(1, std::min(value, 1024)); c->tlas_dirty = !c->instances_h.empty(); }
     else if (n == "fused") rtb::g_tune.fused = value;
     else if (n == "cost_order") rtb::g_tune.cost_order = value;
     else if (n == "queue_keep") rtb::g_tune.queue_keep = std::max(1, std::min(value, 33));
@@ -199,7 +210,20 @@ int rtb_mesh_rebuild(rtb_context* c, int id, const rtb_triangle* tris, int n, in
 {
     if (!c || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive || n < 0 || (n > 0 && !tris))
         return fail(RTB_ERR_INVALID, "rtb_mesh_rebuild: bad argument");
-    return build_mesh(c, c->meshes[id], tris, n, on_device);
+    MeshRec& m = c->meshes[id];
+    const bool had_dynamic_box = m.dynamic && m.cut_valid && m.cut.size() == 6;
+    m.cut_valid = false;
+    int rc = build_mesh(c, m, tris, n, on_device);
+    if (rc != RTB_OK) return rc;
+    m.dynamic = true;
+    // The instance world boxes in the TLAS were made from the OLD geometry.  A deforming mesh keeps them as long as its new
+    // bounds stay inside the (inflated) box they were made from -- no TLAS work in the steady state of an animation --
+    // otherwise the TLAS is rebuilt before the next frame (make_scene).
+    bool covered = had_dynamic_box && n > 0;
+    for (int k = 0; k < 3 && covered; k++) covered = m.bvh.bounds[k] >= m.cut[k] && m.bvh.bounds[k + 3] <= m.cut[k + 3];
+    if (covered) m.cut_valid = true;
+    else for (const auto& in : c->instances_h) if (in.mesh_index == id) { c->tlas_dirty = true; break; }
+    return RTB_OK;
 }
 
 int rtb_mesh_info_get(rtb_context* c, int id, rtb_mesh_info* out)
@@ -270,8 +294,61 @@ int rtb_set_materials(rtb_context* c, const rtb_material* mats, int n)
     return RTB_OK;
 }
 
+// Mesh-space boxes that together cover every triangle of a mesh: the child boxes of a cut through the top levels of its
+// BLAS (read back once per build, <= 85 nodes), opened breadth-first up to `budget` boxes.  An instance's world box is the
+// union of the transformed cut boxes instead of the transformed ROOT box: for a rotated instance the latter is up to
+// sqrt(2) too wide per axis, so neighbouring instances overlap and rays enter BLASes they cannot hit.  A mesh that is being
+// rebuilt per frame (C5) uses its root bounds, inflated by 2 %, so that no read-back or TLAS rebuild sits in the frame loop.
+static int mesh_cut(rtb_context* c, MeshRec& m, int budget)
+{
+    if (m.cut_valid && (m.dynamic || m.cut_budget == budget)) return RTB_OK;
+    m.cut.clear();
+    const float* b = m.bvh.bounds;
+    bool finite = true;
+    for (int k = 0; k < 6; k++) finite = finite && std::isfinite(b[k]);
+    if (m.n > 0 && m.dynamic && finite) {
+        for (int k = 0; k < 3; k++) {
+            const float pad = 0.02f * (b[k + 3] - b[k]) + 1e-6f * std::max(std::fabs(b[k]), std::fabs(b[k + 3]));
+            m.cut.push_back(b[k] - pad);
+        }
+        for (int k = 0; k < 3; k++) m.cut.push_back(b[k + 3] + (b[k] - m.cut[k]));
+    } else if (m.n > 0 && finite && budget > 1 && m.bvh.num_nodes >= 1) {
+        const int K = std::min(m.bvh.num_nodes, 85);
+        std::vector<float4> nd((size_t)K * NODE_F4);
+        CU(cudaMemcpy(nd.data(), m.bvh.nodes, sizeof(float4) * nd.size(), cudaMemcpyDeviceToHost), "read top BLAS levels");
+        struct Box { float lo[3], hi[3]; int ref; };
+        std::vector<Box> open, done;                      // open: FIFO (head index), so the cut is opened level by level
+        auto children = [&](int node) {
+            const float* f = (const float*)&nd[(size_t)node * NODE_F4];
+            for (int k = 0; k < 4; k++) {
+                int ref; memcpy(&ref, f + 24 + k, 4);
+                if (ref == EMPTY_REF) continue;
+                Box x;
+                for (int a = 0; a < 3; a++) { x.lo[a] = f[8 * a + k]; x.hi[a] = f[8 * a + 4 + k]; }
+                x.ref = ref;
+                open.push_back(x);
+            }
+        };
+        children(0);
+        size_t head = 0;
+        while (head < open.size()) {
+            const Box x = open[head++];
+            if (x.ref >= 0 && x.ref < K && done.size() + (open.size() - head) + 4 <= (size_t)budget) children(x.ref);
+            else done.push_back(x);
+        }
+        for (const Box& x : done)
+            for (int a = 0; a < 3; a++) finite = finite && std::isfinite(x.lo[a]) && std::isfinite(x.hi[a]) && x.lo[a] <= x.hi[a];
+        if (finite && !done.empty()) {
+            for (const Box& x : done) { m.cut.insert(m.cut.end(), x.lo, x.lo + 3); m.cut.insert(m.cut.end(), x.hi, x.hi + 3); }
+        }
+    }
+    if (m.cut.empty() && m.n > 0) m.cut.assign(b, b + 6);              // the root box (tiny meshes, budget 1, non-finite bounds)
+    m.cut_valid = true; m.cut_budget = budget; m.cut_serial++;
+    return RTB_OK;
+}
+
 // instance record (see rtb_internal.cuh) + conservative world box
-static int pack_instance(rtb_context* c, const rtb_instance& in, float4 rec[INST_F4], float lo[3], float hi[3])
+static int pack_instance(rtb_context* c, const rtb_instance& in, float4 rec[INST_F4], float lo[3], float hi[3], int* serial)
 {
     if (in.mesh_index < 0 || in.mesh_index >= (int)c->meshes.size() || !c->meshes[in.mesh_index].alive)
         return fail(RTB_ERR_INVALID, "instance refers to a mesh that does not exist");
@@ -292,32 +369,39 @@ static int pack_instance(rtb_context* c, const rtb_instance& in, float4 rec[INST
     rec[3] = make_float4(qi.x, qi.y, qi.z, qi.w);
     rec[4] = make_float4(in.inv_pose.x, in.inv_pose.y, in.inv_pose.z, 0.f);
     rec[5] = make_float4(in.scale[0], in.scale[1], in.scale[2], 0.f);
-    // world box: the ray enters mesh space as m = (R (w - t)) * inv_scale, so w = R^T (m / inv_scale) + t.  Double
-    // precision + padding: the box only culls, it must merely contain every world point the forward map sends inside.
-    const rtb_mesh_info& mi = c->meshes[in.mesh_index].info;
+    // world box: the ray enters mesh space as m = (R (w - t)) * inv_scale, so w = R^T (m / inv_scale) + t = M m + t.  The image
+    // of a box (centre c, half extent h) lies in the box (M c + t) +- |M| h.  Double precision + padding: the box only culls,
+    // it must merely contain every world point the forward map sends inside.
+    MeshRec& mesh = c->meshes[in.mesh_index];
+    int rc = mesh_cut(c, mesh, c->opt_inst_cut);
+    if (rc != RTB_OK) return rc;
+    *serial = mesh.cut_serial;
     float Rf[3][3];
     hm::euler_to_matrix(in.pose.yaw, in.pose.pitch, in.pose.roll, Rf);
+    double M[3][3];
+    for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) M[a][b] = (double)Rf[b][a] / (double)in.inv_scale[b];
     double wlo[3] = { 1e300, 1e300, 1e300 }, whi[3] = { -1e300, -1e300, -1e300 };
-    double mag = 0;
-    for (int k = 0; k < 8; k++) {
-        double m[3];
+    for (size_t o = 0; o + 6 <= mesh.cut.size(); o += 6) {
+        const float* x = &mesh.cut[o];
+        double ctr[3], half[3];
+        for (int b = 0; b < 3; b++) { ctr[b] = 0.5 * ((double)x[b] + (double)x[b + 3]); half[b] = 0.5 * ((double)x[b + 3] - (double)x[b]); }
         for (int a = 0; a < 3; a++) {
-            double v = ((k >> a) & 1) ? mi.bounds_max[a] : mi.bounds_min[a];
-            m[a] = v / (double)in.inv_scale[a];
-        }
-        for (int a = 0; a < 3; a++) {
-            double w = Rf[0][a] * m[0] + Rf[1][a] * m[1] + Rf[2][a] * m[2] + (&in.pose.x)[a];
-            wlo[a] = std::min(wlo[a], w); whi[a] = std::max(whi[a], w);
-            mag = std::max(mag, std::fabs(w));
+            const double wc = M[a][0] * ctr[0] + M[a][1] * ctr[1] + M[a][2] * ctr[2] + (double)(&in.pose.x)[a];
+            const double wh = std::fabs(M[a][0]) * half[0] + std::fabs(M[a][1]) * half[1] + std::fabs(M[a][2]) * half[2];
+            wlo[a] = std::min(wlo[a], wc - wh); whi[a] = std::max(whi[a], wc + wh);
         }
     }
-    if (mi.num_triangles == 0) { for (int a = 0; a < 3; a++) wlo[a] = whi[a] = (&in.pose.x)[a]; mag = 0; }   // empty BLAS: a point
+    double mag = 0;
+    for (int a = 0; a < 3; a++) mag = std::max(mag, std::max(std::fabs(wlo[a]), std::fabs(whi[a])));
+    if (mesh.cut.empty()) { for (int a = 0; a < 3; a++) wlo[a] = whi[a] = (&in.pose.x)[a]; mag = 0; }   // empty BLAS: a point
     const double pad = 1e-4 * mag + 1e-5;
     for (int a = 0; a < 3; a++) { lo[a] = (float)(wlo[a] - pad); hi[a] = (float)(whi[a] + pad); }
     return RTB_OK;
 }
 
-static int rebuild_tlas(rtb_context* c)
+// Packs the instances whose record or mesh cut changed (all of them when `only` < 0 or the count changed), uploads, and
+// rebuilds the TLAS on the device.
+static int rebuild_tlas(rtb_context* c, int only)
 {
     const int n = (int)c->instances_h.size();
     const int cap = std::max(n, 1);
@@ -331,19 +415,29 @@ static int rebuild_tlas(rtb_context* c)
         CU(cudaMalloc((void**)&c->ibox_max, sizeof(float4) * (size_t)cap), "cudaMalloc instance boxes");
         c->inst_cap = cap;
     }
-    std::vector<float4> rec((size_t)cap * INST_F4), lo(cap), hi(cap);
+    const bool all = only < 0 || (int)c->inst_serial.size() != n;
+    if (all) {
+        c->inst_rec_h.assign((size_t)cap * INST_F4, make_float4(0.f, 0.f, 0.f, 0.f));
+        c->ibox_lo_h.assign(cap, make_float4(0.f, 0.f, 0.f, 0.f)); c->ibox_hi_h.assign(cap, make_float4(0.f, 0.f, 0.f, 0.f));
+        c->inst_serial.assign(n, -1);
+    }
     for (int i = 0; i < n; i++) {
+        const int mi = c->instances_h[i].mesh_index;
+        const bool fresh = !all && i != only && mi >= 0 && mi < (int)c->meshes.size() && c->meshes[mi].alive && c->meshes[mi].cut_valid &&
+                           (c->meshes[mi].dynamic || c->meshes[mi].cut_budget == c->opt_inst_cut) && c->meshes[mi].cut_serial == c->inst_serial[i];
+        if (fresh) continue;
         float l[3], h[3];
-        int rc = pack_instance(c, c->instances_h[i], &rec[(size_t)i * INST_F4], l, h);
-        if (rc != RTB_OK) return rc;
-        lo[i] = make_float4(l[0], l[1], l[2], 0.f); hi[i] = make_float4(h[0], h[1], h[2], 0.f);
+        int rc = pack_instance(c, c->instances_h[i], &c->inst_rec_h[(size_t)i * INST_F4], l, h, &c->inst_serial[i]);
+        if (rc != RTB_OK) { c->inst_serial.clear(); return rc; }
+        c->ibox_lo_h[i] = make_float4(l[0], l[1], l[2], 0.f); c->ibox_hi_h[i] = make_float4(h[0], h[1], h[2], 0.f);
     }
     if (n > 0) {
-        CU(cudaMemcpy(c->inst_d, rec.data(), sizeof(float4) * INST_F4 * (size_t)n, cudaMemcpyHostToDevice), "instances upload");
-        CU(cudaMemcpy(c->ibox_min, lo.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
-        CU(cudaMemcpy(c->ibox_max, hi.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
+        CU(cudaMemcpy(c->inst_d, c->inst_rec_h.data(), sizeof(float4) * INST_F4 * (size_t)n, cudaMemcpyHostToDevice), "instances upload");
+        CU(cudaMemcpy(c->ibox_min, c->ibox_lo_h.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
+        CU(cudaMemcpy(c->ibox_max, c->ibox_hi_h.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
     }
     CU(build_bvh(c->ibox_min, c->ibox_max, n, 1, 32, c->tlas, c->ws, 0), "build TLAS");
+    c->tlas_dirty = false;
     return RTB_OK;
 }
 
@@ -352,7 +446,7 @@ int rtb_set_instances(rtb_context* c, const rtb_instance* insts, int n)
     if (!c || n < 0 || (n > 0 && !insts)) return fail(RTB_ERR_INVALID, "rtb_set_instances: bad argument");
     CU(cudaSetDevice(c->device), "cudaSetDevice");
     c->instances_h.assign(insts, insts + n);
-    return rebuild_tlas(c);
+    return rebuild_tlas(c, -1);
 }
 
 int rtb_update_instance(rtb_context* c, int index, const rtb_instance* inst)
@@ -360,7 +454,7 @@ int rtb_update_instance(rtb_context* c, int index, const rtb_instance* inst)
     if (!c || !inst || index < 0 || index >= (int)c->instances_h.size()) return fail(RTB_ERR_INVALID, "rtb_update_instance: bad argument");
     CU(cudaSetDevice(c->device), "cudaSetDevice");
     c->instances_h[index] = *inst;
-    return rebuild_tlas(c);
+    return rebuild_tlas(c, index);
 }
 
 // ------------------------------------------------------------------ render
@@ -374,6 +468,9 @@ static float bounds_extent(const float b[6], int n)
 static int make_scene(rtb_context* c, SceneDev& sc)
 {
     if (!c->tlas.nodes) return fail(RTB_ERR_STATE, "render: no instances set (call rtb_set_instances)");
+    for (const auto& in : c->instances_h)
+        if (!c->meshes[in.mesh_index].alive) return fail(RTB_ERR_STATE, "render: an instance refers to a destroyed mesh");
+    if (c->tlas_dirty) { int rc = rebuild_tlas(c, (int)c->instances_h.size()); if (rc != RTB_OK) return rc; }   // stale boxes only
     if (c->mesh_table_dirty) {
         const int n = (int)c->meshes.size(), cap = std::max(n, 1);
         if (c->meshes_cap < cap) {
@@ -390,8 +487,6 @@ static int make_scene(rtb_context* c, SceneDev& sc)
         CU(cudaMemcpy(c->meshes_d, t.data(), sizeof(MeshDev) * (size_t)cap, cudaMemcpyHostToDevice), "mesh table upload");
         c->mesh_table_dirty = false;
     }
-    for (const auto& in : c->instances_h)
-        if (!c->meshes[in.mesh_index].alive) return fail(RTB_ERR_STATE, "render: an instance refers to a destroyed mesh");
     sc.tlas_nodes = c->tlas.nodes; sc.tlas_index = (const int*)c->tlas.order; sc.inst = c->inst_d; sc.meshes = c->meshes_d;
     sc.materials = c->materials_d; sc.num_instances = (int)c->instances_h.size(); sc.num_materials = (int)c->materials_h.size();
     sc.tlas_extent = bounds_extent(c->tlas.bounds, sc.num_instances);
