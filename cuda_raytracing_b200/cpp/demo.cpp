@@ -4,10 +4,14 @@
 // (kernel.cu:30-49) become a binary PPM (headless presentation); the git-ignored calibration_* assets
 // become any OBJ (and optional PPM texture) given on the command line.
 //
-//   demo <mesh.obj> [out.ppm] [frames] [mode 0..3] [width height] [texture.ppm]
+// When the output name ends in .png the frame loop presents like the reference's: display_image after every frame (FPS overlay,
+// PNG rewritten each frame, kernel.cu:30-43,288) with keys and mouse events replayed from a script (presentation.hpp).
+//
+//   demo <mesh.obj> [out.ppm|out.png] [frames] [mode 0..3] [width height] [texture.ppm|-] [input-script.txt]
 #include "Camera.h"
 #include "Scene.h"
 #include "OBJLoader.hpp"
+#include "presentation.hpp"
 #include <chrono>
 
 static void write_ppm(const char* path, const uchar3* d_img, int width, int height, size_t pitch)
@@ -24,8 +28,12 @@ static void write_ppm(const char* path, const uchar3* d_img, int width, int heig
 
 int main(int argc, char** argv)
 {
-    if (argc < 2) { std::cerr << "usage: demo <mesh.obj> [out.ppm] [frames] [mode] [width height] [texture.ppm]" << std::endl; return 2; }
+    if (argc < 2) { std::cerr << "usage: demo <mesh.obj> [out.ppm|out.png] [frames] [mode] [width height] [texture.ppm|-] [input-script.txt]" << std::endl; return 2; }
     const char* out = argc > 2 ? argv[2] : "out.ppm";
+    const std::string out_s(out);
+    const bool present = out_s.size() > 4 && out_s.compare(out_s.size() - 4, 4, ".png") == 0;
+    if (present) presentation::out_path() = out_s;
+    if (argc > 8 && !presentation::script().load(argv[8])) { std::cerr << "cannot read " << argv[8] << std::endl; return 1; }
     const int frames = argc > 3 ? atoi(argv[3]) : 100;
     const int mode = argc > 4 ? atoi(argv[4]) : 0;
     int width = 1920, height = 1080;                                    // kernel.cu:155-156
@@ -48,7 +56,7 @@ int main(int argc, char** argv)
     Material matte = Material();
     matte.albedo = make_float3(0.9, 0.9, 0.9);
     matte.roughness = 0.3;
-    if (argc > 7) matte.upload_texture(std::string(argv[7]));
+    if (argc > 7 && std::string(argv[7]) != "-") matte.upload_texture(std::string(argv[7]));
     scene.add_material(matte);
 
     MeshPrimitive mesh = OBJLoader::load(argv[1]);
@@ -68,6 +76,8 @@ int main(int argc, char** argv)
     uchar3* d_img2; size_t pitch2;
     cudaMallocPitch(&d_img2, &pitch2, width * sizeof(uchar3), height);
 
+    MouseParams mouse_state;                                            // kernel.cu:255-257
+    mouse_state.pose = &camera.pose;
     float angle = 0.0f;
     double fps = 0.0;
     for (int l = 0; l < frames; l++) {
@@ -82,8 +92,12 @@ int main(int argc, char** argv)
         if (err != cudaSuccess) std::cerr << "CUDA error: " << cudaGetErrorString(err) << std::endl;
         fps = 1.0 / std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         if (l % 10 == 0 || l == frames - 1) std::cout << "FPS: " << fps << "\n";
+        if (present) {
+            display_image(d_img, width, height, pitch, fps, mouse_state);  // kernel.cu:288
+            std::cout << "pose: "; transforms::print(camera.pose);
+        }
     }
-    write_ppm(out, d_img, width, height, pitch);
+    if (!present) write_ppm(out, d_img, width, height, pitch);
     cudaFree(d_img);
     cudaFree(d_img2);
     return 0;
