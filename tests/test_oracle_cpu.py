@@ -312,3 +312,64 @@ def test_band_rows_partition():
         for world in (1, 2, 3, 4, 8):
             rows = torch.cat([tiles.rank_rows(H, r, world) for r in range(world)])
             assert sorted(rows.tolist()) == list(range(H))
+
+
+def test_headless_presentation_script_overlay_png(oracle, tmp_path):
+    """presentation.hpp (kernel.cu:19-139 without a window): scripted WASD steps and mouse-look reproduce the reference's pose
+    arithmetic (checked with the oracle's invert_lre / apply_euler), the PNG decodes to the frame plus a green FPS overlay."""
+    import struct
+    import zlib
+    cpp = os.path.join(ROOT, "cuda_raytracing_b200", "cpp")
+    subprocess.check_call(["make", "-C", cpp, "-s"])
+    script = tmp_path / "in.txt"
+    script.write_text("# frame 0: drag\ndown 100 100\nmove 100 100\nmove 160 70\nup 160 70\nmove 300 300\nframe\nkey w\nkey d\nframe\nkey s\nkey a\nkey x\nkey q\nkey w\n")
+    png = tmp_path / "o.png"
+    W, H = 330, 48
+    r = subprocess.run([os.path.join(cpp, "presentation_test"), str(script), "9", str(png), str(W), str(H), "12.5"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.strip().split("\n")
+    assert lines[-1] == "quit" and len(lines) == 9                               # frames 0..7, then 'q' ends the loop
+    poses = [np.array(l.split()[1:], np.float64).astype(np.float32) for l in lines[:-1]]
+
+    def step(p, v):                                                              # kernel.cu:54-62
+        ip = oracle.invert_lre(p)
+        d = np.array(v, np.float32) - np.array(ip[:3], np.float32)
+        return oracle.apply_euler(np.array(ip[3:], np.float32), d)
+
+    p = np.array([-1, -4, 2, 0, 0, 0], np.float32)
+    p[3] = np.float32(np.float64(p[3]) + 60 * 0.001)                             # kernel.cu:131-132: only while the button is down
+    p[4] = np.float32(np.float64(p[4]) + (-30) * -0.001)
+    assert np.array_equal(poses[0], p), (poses[0], p)
+    want = [p.copy()]
+    for key in "wd-saxq":                                                        # one key per frame (waitKey); '-' = the bare `frame` line
+        v = {"w": (0, 0.1, 0), "s": (0, -0.1, 0), "a": (-0.1, 0, 0), "d": (0.1, 0, 0)}.get(key)   # 'x' and 'q' move nothing
+        if v is not None:
+            p[:3] = step(p, v)
+        want.append(p.copy())
+    for f, (got, w) in enumerate(zip(poses, want)):
+        assert np.allclose(got, w, rtol=0, atol=2e-6), (f, got, w)
+    assert len(poses) == 8 == len(want) and not np.array_equal(poses[5], poses[4])
+
+    raw = png.read_bytes()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, ihdr = 8, b"", None
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(typ + body)
+        if typ == b"IHDR":
+            ihdr = struct.unpack(">IIBBBBB", body)
+        elif typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    assert ihdr == (W, H, 8, 2, 0, 0, 0)
+    rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(H, 1 + 3 * W)
+    assert np.all(rows[:, 0] == 0)
+    rgb = rows[:, 1:].reshape(H, W, 3)
+    yy, xx = np.mgrid[0:H, 0:W]
+    frame = np.stack([(xx + yy) & 0xFF, yy & 0x7F, xx & 0xFF], axis=2).astype(np.uint8)    # the test image, as RGB
+    overlay = np.any(rgb != frame, axis=2)
+    assert overlay.any() and np.all(rgb[overlay] == (0, 255, 0))
+    ys, xs = np.nonzero(overlay)
+    assert ys.min() >= 9 and ys.max() <= 29 and xs.min() >= 10 and xs.max() < 10 + 18 * len("FPS: 12.500000")
+    assert overlay[9:30, 10:25].all(axis=1)[0]                                   # top bar of the 'F'
