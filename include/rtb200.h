@@ -97,12 +97,16 @@ RTB_API int rtb_context_create(int device, rtb_context** out);
 RTB_API void rtb_context_destroy(rtb_context* ctx);
 RTB_API const char* rtb_last_error(void);
 RTB_API int rtb_version(void);
-RTB_API int rtb_set_option(rtb_context* ctx, const char* name, int value);   /* "counters", "leaf_size", "persistent" */
+RTB_API int rtb_set_option(rtb_context* ctx, const char* name, int value);   /* names and defaults: INTEGRATION.md, "Run-time options" */
 
 /* ---- BLAS: replaces MeshPrimitive::MeshPrimitive/build_bvh (MeshPrimitive.cpp:5-15,38-56),
  *      BVHTree::fill (BVHTree.hpp:203-292) and MeshPrimitive::to_device / BVHTree::compile_tree
  *      (MeshPrimitive.cpp:17-36, BVHTree.hpp:364-383) with an on-device LBVH build. ------------- */
 RTB_API int rtb_mesh_create(rtb_context* ctx, const rtb_triangle* tris, int n, int tris_on_device, int* mesh_id);
+/* Rebuilds a BLAS in place from new triangles (deforming geometry; the reference has no such call).  Instances of the mesh
+ * keep working: when the new bounds leave the world boxes the TLAS was built from, the TLAS is rebuilt before the next
+ * frame.  Like every scene-changing call it runs on the default stream and returns when the device has finished; a frame
+ * still in flight on a NON-blocking stream must be waited for first (the reference has one stream and the same rule). */
 RTB_API int rtb_mesh_rebuild(rtb_context* ctx, int mesh_id, const rtb_triangle* tris, int n, int tris_on_device);
 RTB_API int rtb_mesh_info_get(rtb_context* ctx, int mesh_id, rtb_mesh_info* out);
 RTB_API int rtb_mesh_destroy(rtb_context* ctx, int mesh_id);
@@ -116,7 +120,7 @@ RTB_API int rtb_texture_upload(rtb_context* ctx, const unsigned char* bgr_host, 
                                unsigned char** dev_ptr, size_t* pitch);
 RTB_API int rtb_set_materials(rtb_context* ctx, const rtb_material* mats, int n);
 RTB_API int rtb_set_instances(rtb_context* ctx, const rtb_instance* insts, int n);      /* builds the TLAS */
-RTB_API int rtb_update_instance(rtb_context* ctx, int index, const rtb_instance* inst);  /* re-fits the TLAS */
+RTB_API int rtb_update_instance(rtb_context* ctx, int index, const rtb_instance* inst);  /* re-packs this instance, rebuilds the TLAS */
 
 /* ---- render: replaces Camera::render_scene + the render kernel (Camera.cu:18-41, raycast.cu:146-297).
  *      img is a caller-owned DEVICE pointer, BGR uchar3 rows `pitch` bytes apart (kernel.cu:247-253).
