@@ -138,6 +138,7 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     if (n == "counters") c->opt_counters = value;
     else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
     else if (n == "key_bits") c->opt_key_bits = value;
+    else if (n == "sah_node") rtb::g_sah_node_cost = 0.001f * (float)std::max(1, std::min(value, 100000));
     else if (n == "inst_cut") { c->opt_inst_cut = std::max(1, std::min(value, 1024)); c->tlas_dirty = !c->instances_h.empty(); }
     else if (n == "fused") rtb::g_tune.fused = value;
     else if (n == "cost_order") rtb::g_tune.cost_order = value;

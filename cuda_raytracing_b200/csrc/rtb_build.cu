@@ -12,6 +12,8 @@
 
 namespace rtb {
 
+float g_sah_node_cost = 1.0f;     // cost of one wide-node child box relative to one triangle test in the SAH leaf decision (option "sah_node", permille)
+
 // ------------------------------------------------------------------ arena
 cudaError_t Arena::reserve(size_t bytes)
 {
@@ -400,7 +402,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     CK(cudaMemcpyAsync(out.order, vals[cur], sizeof(unsigned) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
     CK(cudaMemsetAsync(visit, 0, sizeof(int) * (size_t)n, st));
-    k_fit<<<g, 256, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, 1.0f, 1.0f);
+    k_fit<<<g, 256, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f);
     k_root_sah<<<1, 1, 0, st>>>(nb_max, ctr);
     // level 0 work item: open binary root into wide node 0
     int2 root_item = make_int2(0, 0);

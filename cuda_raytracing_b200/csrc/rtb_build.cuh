@@ -29,6 +29,8 @@ struct BvhResult {
     float sah = 0.f;
 };
 
+extern float g_sah_node_cost;
+
 // Builds a wide BVH over n primitive boxes (device float4 arrays, w ignored).  Asynchronous on `st`
 // except for one small read-back of the build counters at the end.
 cudaError_t build_bvh(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
