@@ -178,9 +178,8 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
         m.tri_cap = (int)nn;
     }
     CU(cudaEventRecord(c->ev0, st), "event");
-    CU(mesh_prim_boxes(tris_d, n, bmin, bmax, st), "k_tri_boxes");
     int key_bits = c->opt_key_bits ? c->opt_key_bits : (n > (1 << 21) ? 64 : 32);
-    CU(build_bvh(bmin, bmax, n, c->opt_leaf, key_bits, m.bvh, c->ws, st), "build_bvh");
+    CU(build_bvh(tris_d, bmin, bmax, n, c->opt_leaf, key_bits, m.bvh, c->ws, st), "build_bvh");
     CU(mesh_emit(tris_d, n, m.bvh.order, m.tri_rec, m.uvs, st), "k_emit_tris");
     CU(cudaEventRecord(c->ev1, st), "event");
     CU(cudaEventSynchronize(c->ev1), "build sync");
@@ -437,7 +436,7 @@ static int rebuild_tlas(rtb_context* c, int only)
         CU(cudaMemcpy(c->ibox_min, c->ibox_lo_h.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
         CU(cudaMemcpy(c->ibox_max, c->ibox_hi_h.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
     }
-    CU(build_bvh(c->ibox_min, c->ibox_max, n, 1, 32, c->tlas, c->ws, 0), "build TLAS");
+    CU(build_bvh(nullptr, c->ibox_min, c->ibox_max, n, 1, 32, c->tlas, c->ws, 0), "build TLAS");
     c->tlas_dirty = false;
     return RTB_OK;
 }

@@ -44,18 +44,7 @@ struct BuildCounters {
     unsigned bar;           // grid barrier of the collapse kernel
 };
 
-// ------------------------------------------------------------------ 1. primitive boxes
-// Reads the reference's 72-byte AoS triangles (TrianglePrimitive.hpp:8-11); bounds as BVHTree::grow_to_include (175-190).
-__global__ void k_tri_boxes(const rtb_triangle* __restrict__ tris, int n, float4* __restrict__ bmin, float4* __restrict__ bmax)
-{
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float* v = (const float*)(tris + i);
-    float x0 = v[0], y0 = v[1], z0 = v[2], x1 = v[3], y1 = v[4], z1 = v[5], x2 = v[6], y2 = v[7], z2 = v[8];
-    bmin[i] = make_float4(fminf(fminf(x0, x1), x2), fminf(fminf(y0, y1), y2), fminf(fminf(z0, z1), z2), 0.f);
-    bmax[i] = make_float4(fmaxf(fmaxf(x0, x1), x2), fmaxf(fmaxf(y0, y1), y2), fmaxf(fmaxf(z0, z1), z2), 0.f);
-}
-
+// ------------------------------------------------------------------ 1. primitive boxes + scene bounds
 __global__ void k_init_counters(BuildCounters* c)
 {
     int t = threadIdx.x;
@@ -65,32 +54,75 @@ __global__ void k_init_counters(BuildCounters* c)
     if (t == 72) c->bar = 0u;
 }
 
-__global__ void __launch_bounds__(256) k_scene_bounds(const float4* __restrict__ bmin, const float4* __restrict__ bmax, int n, BuildCounters* c)
+// Scene and centroid bounds of n boxes: BB_PER boxes per thread (all loads issued before the first use), reduced per warp
+// by shuffles, per block through shared memory, one atomic set per block.
+// TRIS: the boxes are not read but MADE here, from the reference's 72-byte AoS triangles (TrianglePrimitive.hpp:8-11; bounds as
+// BVHTree::grow_to_include, 175-190), and written out -- one pass over the triangles instead of a box pass plus a second
+// pass that re-reads 32 bytes per primitive just to reduce them.
+constexpr int BB_PER = 4;
+template <bool TRIS>
+__global__ void __launch_bounds__(256) k_scene_bounds(const rtb_triangle* __restrict__ tris, float4* __restrict__ bmin, float4* __restrict__ bmax,
+                                                      int n, BuildCounters* c)
 {
-    float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
-    float clo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, chi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        float4 a = bmin[i], b = bmax[i];
-        float av[3] = { a.x, a.y, a.z }, bv[3] = { b.x, b.y, b.z };
+    __shared__ float red[8][12];
+    float acc[12];                                  // lo xyz, hi xyz, centroid lo xyz, centroid hi xyz
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
-            lo[k] = fminf(lo[k], av[k]); hi[k] = fmaxf(hi[k], bv[k]);
-            float cc = 0.5f * (av[k] + bv[k]);
-            clo[k] = fminf(clo[k], cc); chi[k] = fmaxf(chi[k], cc);
+    for (int k = 0; k < 3; k++) { acc[k] = FLT_MAX; acc[3 + k] = -FLT_MAX; acc[6 + k] = FLT_MAX; acc[9 + k] = -FLT_MAX; }
+    const int base = blockIdx.x * (256 * BB_PER) + threadIdx.x;
+    float4 a[BB_PER], b[BB_PER];
+    if (TRIS) {
+        float v[BB_PER][9];
+#pragma unroll
+        for (int j = 0; j < BB_PER; j++) {
+            const int i = base + j * 256;
+            if (i < n) {
+                const float* t = (const float*)(tris + i);
+#pragma unroll
+                for (int k = 0; k < 9; k++) v[j][k] = __ldg(t + k);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < BB_PER; j++) {
+            const int i = base + j * 256;
+            if (i < n) {
+                a[j] = make_float4(fminf(fminf(v[j][0], v[j][3]), v[j][6]), fminf(fminf(v[j][1], v[j][4]), v[j][7]), fminf(fminf(v[j][2], v[j][5]), v[j][8]), 0.f);
+                b[j] = make_float4(fmaxf(fmaxf(v[j][0], v[j][3]), v[j][6]), fmaxf(fmaxf(v[j][1], v[j][4]), v[j][7]), fmaxf(fmaxf(v[j][2], v[j][5]), v[j][8]), 0.f);
+                bmin[i] = a[j]; bmax[i] = b[j];
+            }
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < BB_PER; j++) { const int i = base + j * 256; if (i < n) { a[j] = bmin[i]; b[j] = bmax[i]; } }
+    }
+#pragma unroll
+    for (int j = 0; j < BB_PER; j++) {
+        if (base + j * 256 < n) {
+            const float av[3] = { a[j].x, a[j].y, a[j].z }, bv[3] = { b[j].x, b[j].y, b[j].z };
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const float cc = 0.5f * (av[k] + bv[k]);
+                acc[k] = fminf(acc[k], av[k]); acc[3 + k] = fmaxf(acc[3 + k], bv[k]);
+                acc[6 + k] = fminf(acc[6 + k], cc); acc[9 + k] = fmaxf(acc[9 + k], cc);
+            }
         }
     }
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
+    for (int k = 0; k < 12; k++) {
+        const bool is_min = (k < 3) || (k >= 6 && k < 9);
         for (int o = 16; o > 0; o >>= 1) {
-            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
-            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
-            clo[k] = fminf(clo[k], __shfl_xor_sync(0xffffffffu, clo[k], o));
-            chi[k] = fmaxf(chi[k], __shfl_xor_sync(0xffffffffu, chi[k], o));
+            const float other = __shfl_xor_sync(0xffffffffu, acc[k], o);
+            acc[k] = is_min ? fminf(acc[k], other) : fmaxf(acc[k], other);
         }
-        if ((threadIdx.x & 31) == 0) {
-            atomicMin(&c->bounds[k], f2ord(lo[k])); atomicMax(&c->bounds[k + 3], f2ord(hi[k]));
-            atomicMin(&c->cbounds[k], f2ord(clo[k])); atomicMax(&c->cbounds[k + 3], f2ord(chi[k]));
-        }
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][k] = acc[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        const int k = threadIdx.x;
+        const bool is_min = (k < 3) || (k >= 6 && k < 9);
+        float r = red[0][k];
+        for (int w = 1; w < 8; w++) r = is_min ? fminf(r, red[w][k]) : fmaxf(r, red[w][k]);
+        int* dst = k < 6 ? &c->bounds[k] : &c->cbounds[k - 6];
+        if (is_min) atomicMin(dst, f2ord(r)); else atomicMax(dst, f2ord(r));
     }
 }
 
@@ -182,12 +214,23 @@ __device__ __forceinline__ float half_area(float4 a, float4 b)
     return x * (y + z) + y * z;
 }
 
-__global__ void k_fit(const float4* __restrict__ bmin, const float4* __restrict__ bmax, const unsigned* __restrict__ order, int n,
+// One thread per leaf climbs towards the root; the second thread to arrive at a node fits it (Karras 2012).  A block owns
+// FIT_CHUNK consecutive leaves of the sorted order, and every node whose leaf range lies inside the block's chunk -- all but
+// a few thousandths of the nodes -- is handled without leaving the SM: arrival counters and child boxes in shared memory, a
+// block-level fence instead of a device-wide one (the box still goes to HBM once, for k_collapse).  Only nodes that span two
+// chunks take the global path: device fence, L2 atomic, child boxes read back through L2.
+constexpr int FIT_CHUNK = 256;
+__global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bmin, const float4* __restrict__ bmax, const unsigned* __restrict__ order, int n,
                       const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
                       const int2* __restrict__ range, float4* nb_min, float4* nb_max, int* visit,
                       unsigned char* __restrict__ flags, int max_leaf, float c_node, float c_tri)
 {
-    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ float4 s_min[2 * FIT_CHUNK], s_max[2 * FIT_CHUNK];    // [0, CHUNK): internal node id - chunk_lo; [CHUNK, 2 CHUNK): leaf - chunk_lo
+    __shared__ int s_visit[FIT_CHUNK];
+    const int chunk_lo = blockIdx.x * FIT_CHUNK, chunk_hi = min(chunk_lo + FIT_CHUNK, n) - 1;
+    s_visit[threadIdx.x] = 0;
+    __syncthreads();
+    const int j = chunk_lo + threadIdx.x;
     if (j >= n) return;
     unsigned p = order[j];
     float4 a = bmin[p], b = bmax[p];
@@ -195,23 +238,36 @@ __global__ void k_fit(const float4* __restrict__ bmin, const float4* __restrict_
     a.w = ha; b.w = ha * c_tri;
     int id = n - 1 + j;
     nb_min[id] = a; nb_max[id] = b;
+    s_min[FIT_CHUNK + threadIdx.x] = a; s_max[FIT_CHUNK + threadIdx.x] = b;
     flags[id] = 1;
     int cur = parent[id];
     while (cur >= 0) {
-        __threadfence();
-        if (atomicAdd(&visit[cur], 1) == 0) return;     // first arrival: the sibling finishes the node
-        int lc = left[cur], rc = right[cur];
-        float4 la = __ldcg(nb_min + lc), lb = __ldcg(nb_max + lc), ra = __ldcg(nb_min + rc), rb = __ldcg(nb_max + rc);
+        const int2 rg = range[cur];
+        const bool local = rg.x >= chunk_lo && rg.y <= chunk_hi;
+        float4 la, lb, ra, rb;
+        const int lc = left[cur], rc = right[cur];
+        if (local) {
+            __threadfence_block();
+            if (atomicAdd(&s_visit[cur - chunk_lo], 1) == 0) return;     // first arrival: the sibling finishes the node
+            __threadfence_block();
+            const int li = lc >= n - 1 ? FIT_CHUNK + (lc - (n - 1)) - chunk_lo : lc - chunk_lo;
+            const int ri = rc >= n - 1 ? FIT_CHUNK + (rc - (n - 1)) - chunk_lo : rc - chunk_lo;
+            la = s_min[li]; lb = s_max[li]; ra = s_min[ri]; rb = s_max[ri];
+        } else {
+            __threadfence();
+            if (atomicAdd(&visit[cur], 1) == 0) return;
+            la = __ldcg(nb_min + lc); lb = __ldcg(nb_max + lc); ra = __ldcg(nb_min + rc); rb = __ldcg(nb_max + rc);
+        }
         float4 mn = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.f);
         float4 mx = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.f);
         float h = half_area(mn, mx);
-        int2 rg = range[cur];
         int cnt = rg.y - rg.x + 1;
         float c_split = c_node * h + lb.w + rb.w;
         float c_leaf = cnt <= max_leaf ? c_tri * h * (float)cnt : FLT_MAX;
         bool leaf = cnt <= max_leaf && !(c_leaf > c_split);   // never a leaf above max_leaf, whatever the costs (inf/NaN boxes)
         mn.w = h; mx.w = leaf ? c_leaf : c_split;
         nb_min[cur] = mn; nb_max[cur] = mx;
+        if (local) { s_min[cur - chunk_lo] = mn; s_max[cur - chunk_lo] = mx; }
         flags[cur] = leaf ? 1 : 0;
         cur = parent[cur];
     }
@@ -360,18 +416,12 @@ __global__ void k_emit_tris(const rtb_triangle* __restrict__ tris, int n, const 
     r[1] = make_float4(A.x, A.y, A.z, xdot(e0, e0));
     r[2] = make_float4(e0.x, e0.y, e0.z, xdot(e0, e1));
     r[3] = make_float4(e1.x, e1.y, e1.z, xdot(e1, e1));
-    float2* u = uvs + (size_t)p * 3;
+    float2* u = uvs + (size_t)j * 3;                        // in leaf order, like the records: coalesced here, and the shader has the slot
     u[0] = make_float2(t[12], t[13]); u[1] = make_float2(t[14], t[15]); u[2] = make_float2(t[16], t[17]);
 }
 
 // ------------------------------------------------------------------ host side
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
-
-cudaError_t mesh_prim_boxes(const rtb_triangle* tris_dev, int n, float4* bmin, float4* bmax, cudaStream_t st)
-{
-    if (n > 0) k_tri_boxes<<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, bmin, bmax);
-    return cudaGetLastError();
-}
 
 cudaError_t mesh_emit(const rtb_triangle* tris_dev, int n, const unsigned* order, float4* tri_rec, float2* uvs, cudaStream_t st)
 {
@@ -402,7 +452,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     CK(cudaMemcpyAsync(out.order, vals[cur], sizeof(unsigned) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
     CK(cudaMemsetAsync(visit, 0, sizeof(int) * (size_t)n, st));
-    k_fit<<<g, 256, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f);
+    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f);
     k_root_sah<<<1, 1, 0, st>>>(nb_max, ctr);
     // level 0 work item: open binary root into wide node 0
     int2 root_item = make_int2(0, 0);
@@ -425,7 +475,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     return cudaGetLastError();
 }
 
-cudaError_t build_bvh(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out, Arena& ws,
+cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out, Arena& ws,
                       cudaStream_t st)
 {
     // outputs (grow-only)
@@ -451,7 +501,11 @@ cudaError_t build_bvh(const float4* bmin, const float4* bmax, int n, int max_lea
     ws.reset();
     BuildCounters* ctr = ws.take<BuildCounters>(1);
     k_init_counters<<<1, 96, 0, st>>>(ctr);
-    if (n > 0) k_scene_bounds<<<std::min((n + 255) / 256, 148 * 8), 256, 0, st>>>(bmin, bmax, n, ctr);
+    if (n > 0) {
+        const int gb = (n + 256 * BB_PER - 1) / (256 * BB_PER);
+        if (tris_dev) k_scene_bounds<true><<<gb, 256, 0, st>>>(tris_dev, bmin, bmax, n, ctr);
+        else k_scene_bounds<false><<<gb, 256, 0, st>>>(nullptr, bmin, bmax, n, ctr);
+    }
     if (n <= 1) {
         k_trivial_root<<<1, 1, 0, st>>>(out.nodes, bmin, bmax, n);
         if (n == 1) k_iota<<<1, 32, 0, st>>>(out.order, 1);

@@ -31,13 +31,13 @@ struct BvhResult {
 
 extern float g_sah_node_cost;
 
-// Builds a wide BVH over n primitive boxes (device float4 arrays, w ignored).  Asynchronous on `st`
-// except for one small read-back of the build counters at the end.
-cudaError_t build_bvh(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
+// Builds a wide BVH over n primitive boxes (device float4 arrays, w ignored).  With `tris_dev` the boxes are first made from
+// those n triangles (written to bmin/bmax, fused with the scene-bounds reduction); without, bmin/bmax are the input.
+// Asynchronous on `st` except for one small read-back of the build counters at the end.
+cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
                       Arena& ws, cudaStream_t st);
 
 // Triangle-mesh front/back ends.
-cudaError_t mesh_prim_boxes(const rtb_triangle* tris_dev, int n, float4* bmin, float4* bmax, cudaStream_t st);
 cudaError_t mesh_emit(const rtb_triangle* tris_dev, int n, const unsigned* order, float4* tri_rec, float2* uvs, cudaStream_t st);
 
 }  // namespace rtb

@@ -38,7 +38,7 @@ constexpr int BAND_ROWS = 8;        // image rows per multi-GPU band
 struct MeshDev {
     const float4* nodes;            // wide nodes, root = 0
     const float4* tris;             // triangle records in leaf order
-    const float2* uvs;              // 3 x float2 per ORIGINAL triangle index (TrianglePrimitive::uv_coords)
+    const float2* uvs;              // 3 x float2 per triangle in leaf order, like `tris` (TrianglePrimitive::uv_coords)
     int num_triangles;
     float extent;                   // largest |coordinate| of the mesh bounds (slab-test error bound)
 };

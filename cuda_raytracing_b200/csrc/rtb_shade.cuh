@@ -36,7 +36,7 @@ XF f3 base_colour(const SceneDev& sc, const Hit& h, int material, int mesh)
     const int tw = m->texture_width;
     if (tw > 0) {
         const int th = m->texture_height;
-        const float2* uvp = sc.meshes[mesh].uvs + (size_t)h.prim * 3;
+        const float2* uvp = sc.meshes[mesh].uvs + (size_t)h.slot * 3;
         const float2 uv0 = __ldg(uvp + 0), uv1 = __ldg(uvp + 1), uv2 = __ldg(uvp + 2);
         const float w = xs(xs(1.0f, h.u), h.v);
         const float ux = xa(xa(xm(w, uv0.x), xm(h.v, uv1.x)), xm(h.u, uv2.x));
