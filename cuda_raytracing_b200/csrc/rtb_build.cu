@@ -42,6 +42,7 @@ struct BuildCounters {
     float sah;
     int qcount[72];         // collapse work-queue sizes per level
     unsigned bar;           // grid barrier of the collapse kernel
+    int top_count;          // nodes handed from k_fit to k_fit_top
 };
 
 // ------------------------------------------------------------------ 1. primitive boxes + scene bounds
@@ -51,7 +52,7 @@ __global__ void k_init_counters(BuildCounters* c)
     if (t < 3) { c->bounds[t] = f2ord(FLT_MAX); c->bounds[t + 3] = f2ord(-FLT_MAX); c->cbounds[t] = f2ord(FLT_MAX); c->cbounds[t + 3] = f2ord(-FLT_MAX); }
     if (t == 0) { c->n_wide = 1; c->n_leaves = 0; c->max_leaf = 0; c->max_level = 0; c->sah = 0.f; }
     if (t < 72) c->qcount[t] = 0;
-    if (t == 72) c->bar = 0u;
+    if (t == 72) { c->bar = 0u; c->top_count = 0; }
 }
 
 // Scene and centroid bounds of n boxes: BB_PER boxes per thread (all loads issued before the first use), reduced per warp
@@ -217,13 +218,15 @@ __device__ __forceinline__ float half_area(float4 a, float4 b)
 // One thread per leaf climbs towards the root; the second thread to arrive at a node fits it (Karras 2012).  A block owns
 // FIT_CHUNK consecutive leaves of the sorted order, and every node whose leaf range lies inside the block's chunk -- all but
 // a few thousandths of the nodes -- is handled without leaving the SM: arrival counters and child boxes in shared memory, a
-// block-level fence instead of a device-wide one (the box still goes to HBM once, for k_collapse).  Only nodes that span two
-// chunks take the global path: device fence, L2 atomic, child boxes read back through L2.
+// block-level fence instead of a device-wide one (the box still goes to HBM once, for k_collapse).  A thread that reaches a
+// node spanning two chunks does not climb on -- those chains are long (device fence, L2 atomic, child boxes back through L2
+// at every level) and one such thread would keep its whole block resident -- it appends the node to a list and leaves;
+// k_fit_top finishes the few nodes above the chunks.
 constexpr int FIT_CHUNK = 256;
 __global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bmin, const float4* __restrict__ bmax, const unsigned* __restrict__ order, int n,
                       const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
                       const int2* __restrict__ range, float4* nb_min, float4* nb_max, int* visit,
-                      unsigned char* __restrict__ flags, int max_leaf, float c_node, float c_tri)
+                      unsigned char* __restrict__ flags, int max_leaf, float c_node, float c_tri, int* __restrict__ top_list, BuildCounters* c)
 {
     __shared__ float4 s_min[2 * FIT_CHUNK], s_max[2 * FIT_CHUNK];    // [0, CHUNK): internal node id - chunk_lo; [CHUNK, 2 CHUNK): leaf - chunk_lo
     __shared__ int s_visit[FIT_CHUNK];
@@ -244,20 +247,14 @@ __global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bm
     while (cur >= 0) {
         const int2 rg = range[cur];
         const bool local = rg.x >= chunk_lo && rg.y <= chunk_hi;
-        float4 la, lb, ra, rb;
+        if (!local) { top_list[atomicAdd(&c->top_count, 1)] = cur; return; }      // both children's threads do this; k_fit_top pairs them up
         const int lc = left[cur], rc = right[cur];
-        if (local) {
-            __threadfence_block();
-            if (atomicAdd(&s_visit[cur - chunk_lo], 1) == 0) return;     // first arrival: the sibling finishes the node
-            __threadfence_block();
-            const int li = lc >= n - 1 ? FIT_CHUNK + (lc - (n - 1)) - chunk_lo : lc - chunk_lo;
-            const int ri = rc >= n - 1 ? FIT_CHUNK + (rc - (n - 1)) - chunk_lo : rc - chunk_lo;
-            la = s_min[li]; lb = s_max[li]; ra = s_min[ri]; rb = s_max[ri];
-        } else {
-            __threadfence();
-            if (atomicAdd(&visit[cur], 1) == 0) return;
-            la = __ldcg(nb_min + lc); lb = __ldcg(nb_max + lc); ra = __ldcg(nb_min + rc); rb = __ldcg(nb_max + rc);
-        }
+        __threadfence_block();
+        if (atomicAdd(&s_visit[cur - chunk_lo], 1) == 0) return;                  // first arrival: the sibling finishes the node
+        __threadfence_block();
+        const int li = lc >= n - 1 ? FIT_CHUNK + (lc - (n - 1)) - chunk_lo : lc - chunk_lo;
+        const int ri = rc >= n - 1 ? FIT_CHUNK + (rc - (n - 1)) - chunk_lo : rc - chunk_lo;
+        const float4 la = s_min[li], lb = s_max[li], ra = s_min[ri], rb = s_max[ri];
         float4 mn = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.f);
         float4 mx = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.f);
         float h = half_area(mn, mx);
@@ -267,9 +264,40 @@ __global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bm
         bool leaf = cnt <= max_leaf && !(c_leaf > c_split);   // never a leaf above max_leaf, whatever the costs (inf/NaN boxes)
         mn.w = h; mx.w = leaf ? c_leaf : c_split;
         nb_min[cur] = mn; nb_max[cur] = mx;
-        if (local) { s_min[cur - chunk_lo] = mn; s_max[cur - chunk_lo] = mx; }
+        s_min[cur - chunk_lo] = mn; s_max[cur - chunk_lo] = mx;
         flags[cur] = leaf ? 1 : 0;
         cur = parent[cur];
+    }
+}
+
+// The nodes above the chunks: one thread per list entry, the classic climb (every node appears twice in the list, once per
+// child; the second arrival fits it and goes on).  The boxes below were written by k_fit, a kernel boundary ago.
+__global__ void __launch_bounds__(256) k_fit_top(const int* __restrict__ top_list, const BuildCounters* __restrict__ c, int n,
+                          const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
+                          const int2* __restrict__ range, float4* nb_min, float4* nb_max, int* visit,
+                          unsigned char* __restrict__ flags, int max_leaf, float c_node, float c_tri)
+{
+    const int count = c->top_count;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < count; e += gridDim.x * blockDim.x) {
+        int cur = top_list[e];
+        while (cur >= 0) {
+            __threadfence();
+            if (atomicAdd(&visit[cur], 1) == 0) break;
+            const int lc = left[cur], rc = right[cur];
+            const int2 rg = range[cur];
+            const float4 la = __ldcg(nb_min + lc), lb = __ldcg(nb_max + lc), ra = __ldcg(nb_min + rc), rb = __ldcg(nb_max + rc);
+            float4 mn = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.f);
+            float4 mx = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.f);
+            float h = half_area(mn, mx);
+            int cnt = rg.y - rg.x + 1;
+            float c_split = c_node * h + lb.w + rb.w;
+            float c_leaf = cnt <= max_leaf ? c_tri * h * (float)cnt : FLT_MAX;
+            bool leaf = cnt <= max_leaf && !(c_leaf > c_split);
+            mn.w = h; mx.w = leaf ? c_leaf : c_split;
+            nb_min[cur] = mn; nb_max[cur] = mx;
+            flags[cur] = leaf ? 1 : 0;
+            cur = parent[cur];
+        }
     }
 }
 
@@ -452,7 +480,9 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     CK(cudaMemcpyAsync(out.order, vals[cur], sizeof(unsigned) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
     CK(cudaMemsetAsync(visit, 0, sizeof(int) * (size_t)n, st));
-    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f);
+    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f,
+                                                                   (int*)q0, ctr);
+    k_fit_top<<<148 * 4, 256, 0, st>>>((const int*)q0, ctr, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f);
     k_root_sah<<<1, 1, 0, st>>>(nb_max, ctr);
     // level 0 work item: open binary root into wide node 0
     int2 root_item = make_int2(0, 0);
