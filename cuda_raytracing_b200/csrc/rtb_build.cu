@@ -222,7 +222,10 @@ __device__ __forceinline__ float half_area(float4 a, float4 b)
 // node spanning two chunks does not climb on -- those chains are long (device fence, L2 atomic, child boxes back through L2
 // at every level) and one such thread would keep its whole block resident -- it appends the node to a list and leaves;
 // k_fit_top finishes the few nodes above the chunks.
-constexpr int FIT_CHUNK = 256;
+#ifndef RTB_FIT_CHUNK
+#define RTB_FIT_CHUNK 256
+#endif
+constexpr int FIT_CHUNK = RTB_FIT_CHUNK;
 __global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bmin, const float4* __restrict__ bmax, const unsigned* __restrict__ order, int n,
                       const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
                       const int2* __restrict__ range, float4* nb_min, float4* nb_max, int* visit,

@@ -8,6 +8,8 @@ sys.path.insert(0, ROOT)
 import torch
 from cuda_raytracing_b200 import api, synth
 
+if os.environ.get("RTB_VARIANT"):                           # A/B a differently compiled library (tools/build_variant.sh)
+    api.LIB_PATH = os.path.join(ROOT, "tools", "variants", os.environ["RTB_VARIANT"])
 N, M = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (1582, 3161)
 rep = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 tris = synth.bumpy_sphere(N, M)
