@@ -179,9 +179,7 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
     }
     CU(cudaEventRecord(c->ev0, st), "event");
     int key_bits = c->opt_key_bits ? c->opt_key_bits : (n > (1 << 21) ? 64 : 32);
-    CU(build_bvh(tris_d, bmin, bmax, n, c->opt_leaf, key_bits, m.bvh, c->ws, st), "build_bvh");
-    CU(mesh_emit(tris_d, n, m.bvh.order, m.tri_rec, m.uvs, st), "k_emit_tris");
-    CU(cudaEventRecord(c->ev1, st), "event");
+    CU(build_bvh(tris_d, bmin, bmax, n, c->opt_leaf, key_bits, m.bvh, c->ws, st, m.tri_rec, m.uvs, c->ev1), "build_bvh");
     CU(cudaEventSynchronize(c->ev1), "build sync");
     float ms = 0.f;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);

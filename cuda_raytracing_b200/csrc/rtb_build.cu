@@ -329,7 +329,13 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned target)
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(128) k_collapse(int2* __restrict__ q0, int2* __restrict__ q1, int n,
+#ifndef RTB_COLLAPSE_MINB
+#define RTB_COLLAPSE_MINB 1
+#endif
+#ifndef RTB_COLLAPSE_CAP
+#define RTB_COLLAPSE_CAP 8
+#endif
+__global__ void __launch_bounds__(128, RTB_COLLAPSE_MINB) k_collapse(int2* __restrict__ q0, int2* __restrict__ q1, int n,
                                                   const int* __restrict__ left, const int* __restrict__ right,
                                                   const int2* __restrict__ range, const float4* __restrict__ nb_min,
                                                   const float4* __restrict__ nb_max, const unsigned char* __restrict__ flags,
@@ -432,13 +438,25 @@ __global__ void k_root_sah(const float4* nb_max, BuildCounters* c) { c->sah = nb
 // ------------------------------------------------------------------ 6. triangle records
 // 64-byte records in leaf order; every derived value uses the unfused ops of point_inside
 // (TrianglePrimitive.hpp:154-162) so the tracer's predicate is bit-identical to the reference's.
+// WIDE: the 72-byte record is fetched with nine 8-byte loads instead of eighteen 4-byte ones (the base pointer must be 8-byte
+// aligned: checked on the host) -- ncu showed the kernel waiting on the load/store queue (lg_throttle), not on HBM.
+template <bool WIDE>
 __global__ void k_emit_tris(const rtb_triangle* __restrict__ tris, int n, const unsigned* __restrict__ order,
                             float4* __restrict__ rec, float2* __restrict__ uvs)
 {
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     unsigned p = order[j];
-    const float* t = (const float*)(tris + p);
+    float t[18];
+    if (WIDE) {
+        const float2* t2 = (const float2*)(tris + p);
+#pragma unroll
+        for (int k = 0; k < 9; k++) { const float2 w = __ldg(t2 + k); t[2 * k] = w.x; t[2 * k + 1] = w.y; }
+    } else {
+        const float* t1 = (const float*)(tris + p);
+#pragma unroll
+        for (int k = 0; k < 18; k++) t[k] = __ldg(t1 + k);
+    }
     f3 A = mk3(t[0], t[1], t[2]), B = mk3(t[3], t[4], t[5]), C = mk3(t[6], t[7], t[8]);
     f3 nrm = mk3(t[9], t[10], t[11]);
     f3 e0 = xsub(C, A), e1 = xsub(B, A);
@@ -453,12 +471,6 @@ __global__ void k_emit_tris(const rtb_triangle* __restrict__ tris, int n, const 
 
 // ------------------------------------------------------------------ host side
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
-
-cudaError_t mesh_emit(const rtb_triangle* tris_dev, int n, const unsigned* order, float4* tri_rec, float2* uvs, cudaStream_t st)
-{
-    if (n > 0) k_emit_tris<<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, order, tri_rec, uvs);
-    return cudaGetLastError();
-}
 
 template <typename K>
 static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
@@ -498,7 +510,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
         CK(cudaGetDevice(&dev));
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_collapse, 128, 0));
-        resident = sms * std::max(1, std::min(per_sm, 8));
+        resident = sms * std::max(1, std::min(per_sm, RTB_COLLAPSE_CAP));
     }
     // cooperative launch: the driver starts the grid only when every CTA can be resident at once, so the grid barrier cannot
     // deadlock against another persistent kernel (a second context building on another stream, a render in flight)
@@ -509,7 +521,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
 }
 
 cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out, Arena& ws,
-                      cudaStream_t st)
+                      cudaStream_t st, float4* tri_rec, float2* uvs, cudaEvent_t done)
 {
     // outputs (grow-only)
     int need_nodes = n > 1 ? n : 1;
@@ -547,6 +559,13 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
     } else {
         CK(build_tree<unsigned>(bmin, bmax, n, max_leaf, 32, out, ws, ctr, st));
     }
+    // triangle records in leaf order: enqueued BEFORE the counters are read back, so the device does not idle while the host
+    // wakes up from the synchronisation below (one host round trip per build instead of two)
+    if (tris_dev && tri_rec && uvs && n > 0) {
+        if (((uintptr_t)tris_dev & 7u) == 0) k_emit_tris<true><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, out.order, tri_rec, uvs);
+        else k_emit_tris<false><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, out.order, tri_rec, uvs);
+    }
+    if (done) CK(cudaEventRecord(done, st));
     BuildCounters h;
     CK(cudaMemcpyAsync(&h, ctr, sizeof h, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
