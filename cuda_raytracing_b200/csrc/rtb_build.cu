@@ -229,7 +229,8 @@ constexpr int FIT_CHUNK = RTB_FIT_CHUNK;
 __global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bmin, const float4* __restrict__ bmax, const unsigned* __restrict__ order, int n,
                       const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
                       const int2* __restrict__ range, float4* nb_min, float4* nb_max, int* visit,
-                      unsigned char* __restrict__ flags, int max_leaf, float c_node, float c_tri, int* __restrict__ top_list, BuildCounters* c)
+                      unsigned char* __restrict__ flags, int4* __restrict__ topo, int max_leaf, float c_node, float c_tri, int* __restrict__ top_list,
+                      BuildCounters* c)
 {
     __shared__ float4 s_min[2 * FIT_CHUNK], s_max[2 * FIT_CHUNK];    // [0, CHUNK): internal node id - chunk_lo; [CHUNK, 2 CHUNK): leaf - chunk_lo
     __shared__ int s_visit[FIT_CHUNK];
@@ -269,6 +270,7 @@ __global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bm
         nb_min[cur] = mn; nb_max[cur] = mx;
         s_min[cur - chunk_lo] = mn; s_max[cur - chunk_lo] = mx;
         flags[cur] = leaf ? 1 : 0;
+        topo[cur] = make_int4(lc, rc, __float_as_int(h), leaf ? 1 : 0);
         cur = parent[cur];
     }
 }
@@ -278,7 +280,7 @@ __global__ void __launch_bounds__(FIT_CHUNK) k_fit(const float4* __restrict__ bm
 __global__ void __launch_bounds__(256) k_fit_top(const int* __restrict__ top_list, const BuildCounters* __restrict__ c, int n,
                           const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
                           const int2* __restrict__ range, float4* nb_min, float4* nb_max, int* visit,
-                          unsigned char* __restrict__ flags, int max_leaf, float c_node, float c_tri)
+                          unsigned char* __restrict__ flags, int4* __restrict__ topo, int max_leaf, float c_node, float c_tri)
 {
     const int count = c->top_count;
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < count; e += gridDim.x * blockDim.x) {
@@ -299,6 +301,7 @@ __global__ void __launch_bounds__(256) k_fit_top(const int* __restrict__ top_lis
             mn.w = h; mx.w = leaf ? c_leaf : c_split;
             nb_min[cur] = mn; nb_max[cur] = mx;
             flags[cur] = leaf ? 1 : 0;
+            topo[cur] = make_int4(lc, rc, __float_as_int(h), leaf ? 1 : 0);
             cur = parent[cur];
         }
     }
@@ -330,7 +333,7 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned target)
 }
 
 #ifndef RTB_COLLAPSE_MINB
-#define RTB_COLLAPSE_MINB 1
+#define RTB_COLLAPSE_MINB 7
 #endif
 #ifndef RTB_COLLAPSE_CAP
 #define RTB_COLLAPSE_CAP 8
@@ -338,7 +341,7 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned target)
 __global__ void __launch_bounds__(128, RTB_COLLAPSE_MINB) k_collapse(int2* __restrict__ q0, int2* __restrict__ q1, int n,
                                                   const int* __restrict__ left, const int* __restrict__ right,
                                                   const int2* __restrict__ range, const float4* __restrict__ nb_min,
-                                                  const float4* __restrict__ nb_max, const unsigned char* __restrict__ flags,
+                                                  const float4* __restrict__ nb_max, const int4* __restrict__ topo,
                                                   float4* __restrict__ nodes, BuildCounters* c)
 {
     const int lane = threadIdx.x & 31;
@@ -356,25 +359,33 @@ __global__ void __launch_bounds__(128, RTB_COLLAPSE_MINB) k_collapse(int2* __res
             const bool active = it < items;
             int2 item = make_int2(0, 0);
             int slot[4] = { 0, 0, 0, 0 }; int ns = 0;
+            // per slot: what the greedy opening needs of its binary node -- (left, right, half area, leaf flag), ONE 16-byte record
+            // written by k_fit (it was four scattered fetches: flags[], nb_min[].w, left[], right[]); area < 0 = cannot be opened
+            int cl[4] = { 0, 0, 0, 0 }, cr[4] = { 0, 0, 0, 0 }; float area[4] = { -1.f, -1.f, -1.f, -1.f };
             bool inner[4] = { false, false, false, false };
             int kc = 0;
             if (active) {
                 item = __ldcg(q_in + it);
-                if (flags[item.x]) { slot[0] = item.x; ns = 1; }             // whole tree is one leaf (tiny meshes)
-                else { slot[0] = left[item.x]; slot[1] = right[item.x]; ns = 2; }
+                // slot k (a run-time index: written through an unrolled select so the arrays stay in registers)
+                auto fetch = [&](int k, int id) {
+                    int l = 0, r = 0; float a = -1.f;
+                    if (id < n - 1) { const int4 t = __ldg(topo + id); l = t.x; r = t.y; a = t.w ? -1.f : fmaxf(__int_as_float(t.z), 0.f); }
+#pragma unroll
+                    for (int q = 0; q < 4; q++) if (q == k) { slot[q] = id; cl[q] = l; cr[q] = r; area[q] = a; }
+                };
+                const int4 t0 = __ldg(topo + item.x);
+                if (t0.w) { fetch(0, item.x); ns = 1; }                      // whole tree is one leaf (tiny meshes)
+                else { fetch(0, t0.x); fetch(1, t0.y); ns = 2; }
                 while (ns < 4) {
-                    int best = -1; float barea = -1.f;
-                    for (int k = 0; k < ns; k++) {
-                        int id = slot[k];
-                        if (id < n - 1 && !flags[id]) { float a = nb_min[id].w; if (a > barea) { barea = a; best = k; } }
-                    }
+                    int best = -1, l = 0, r = 0; float barea = -1.f;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) if (k < ns && area[k] > barea) { barea = area[k]; best = k; l = cl[k]; r = cr[k]; }
                     if (best < 0) break;
-                    int id = slot[best];
-                    slot[best] = left[id];
-                    slot[ns++] = right[id];
+                    fetch(best, l);
+                    fetch(ns++, r);
                 }
 #pragma unroll
-                for (int k = 0; k < 4; k++) { inner[k] = k < ns && slot[k] < n - 1 && !flags[slot[k]]; kc += inner[k] ? 1 : 0; }
+                for (int k = 0; k < 4; k++) { inner[k] = k < ns && area[k] >= 0.f; kc += inner[k] ? 1 : 0; }
             }
             // next level's queue positions for this warp's interior children: exclusive scan + one atomic
             int pre = kc;
@@ -486,6 +497,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     int* visit = ws.take<int>(n);
     float4* nb_min = ws.take<float4>(2 * (size_t)n); float4* nb_max = ws.take<float4>(2 * (size_t)n);
     unsigned char* flags = ws.take<unsigned char>(2 * (size_t)n);
+    int4* topo = ws.take<int4>(n);
     int2* q0 = ws.take<int2>(n); int2* q1 = ws.take<int2>(n);
     if (!q1) return cudaErrorMemoryAllocation;
 
@@ -495,9 +507,9 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     CK(cudaMemcpyAsync(out.order, vals[cur], sizeof(unsigned) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
     CK(cudaMemsetAsync(visit, 0, sizeof(int) * (size_t)n, st));
-    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f,
+    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, flags, topo, max_leaf, g_sah_node_cost, 1.0f,
                                                                    (int*)q0, ctr);
-    k_fit_top<<<148 * 4, 256, 0, st>>>((const int*)q0, ctr, n, left, right, parent, range, nb_min, nb_max, visit, flags, max_leaf, g_sah_node_cost, 1.0f);
+    k_fit_top<<<148 * 4, 256, 0, st>>>((const int*)q0, ctr, n, left, right, parent, range, nb_min, nb_max, visit, flags, topo, max_leaf, g_sah_node_cost, 1.0f);
     k_root_sah<<<1, 1, 0, st>>>(nb_max, ctr);
     // level 0 work item: open binary root into wide node 0
     int2 root_item = make_int2(0, 0);
@@ -515,7 +527,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     // cooperative launch: the driver starts the grid only when every CTA can be resident at once, so the grid barrier cannot
     // deadlock against another persistent kernel (a second context building on another stream, a render in flight)
     float4* nodes_out = out.nodes;
-    void* args[] = { &q0, &q1, &n, &left, &right, &range, &nb_min, &nb_max, &flags, &nodes_out, &ctr };
+    void* args[] = { &q0, &q1, &n, &left, &right, &range, &nb_min, &nb_max, &topo, &nodes_out, &ctr };
     CK(cudaLaunchCooperativeKernel((const void*)k_collapse, dim3(std::min(resident, (n + 127) / 128)), dim3(128), args, 0, st));
     return cudaGetLastError();
 }
@@ -541,7 +553,7 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
     if (max_leaf < 1) max_leaf = 1;
     if (max_leaf > MAX_LEAF) max_leaf = MAX_LEAF;
     const bool wide_keys = key_bits > 32;
-    size_t bytes = 4096 + (size_t)(n + 64) * (size_t)((wide_keys ? 16 : 8) + 8 + 4 * 6 + 8 + 64 + 2 + 16) + (size_t)256 * 4 * ((n + RS_TILE - 1) / RS_TILE + 1) + 64 * 256;
+    size_t bytes = 4096 + (size_t)(n + 64) * (size_t)((wide_keys ? 16 : 8) + 8 + 4 * 6 + 8 + 64 + 2 + 16 + 16) + (size_t)256 * 4 * ((n + RS_TILE - 1) / RS_TILE + 1) + 64 * 256;
     CK(ws.reserve(bytes));
     ws.reset();
     BuildCounters* ctr = ws.take<BuildCounters>(1);
