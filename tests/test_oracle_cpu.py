@@ -239,6 +239,26 @@ def test_cabi_exports_every_declared_symbol(rtb):
     assert set(rtb.EXPORTS) <= set(declared)
 
 
+def test_cabi_rejects_null_arguments_without_a_device(rtb):
+    """Error behaviour of the boundary: every entry point that takes a context returns RTB_ERR_INVALID (-1) and sets
+    rtb_last_error for NULL arguments -- no crash, no device needed."""
+    L = rtb.lib()
+    calls = {
+        "rtb_set_option": (None, b"counters", 1), "rtb_mesh_create": (None, None, 0, 0, None), "rtb_mesh_rebuild": (None, 0, None, 0, 0),
+        "rtb_mesh_info_get": (None, 0, None), "rtb_mesh_destroy": (None, 0), "rtb_mesh_read": (None, 0, 0, None, 0),
+        "rtb_texture_upload": (None, None, 0, 0, None, None), "rtb_set_materials": (None, None, 0), "rtb_set_instances": (None, None, 0),
+        "rtb_update_instance": (None, 0, None), "rtb_render": (None, None, None, 0, None, None), "rtb_render_host": (None, None, None, 0, None),
+        "rtb_synchronize": (None,), "rtb_frame_stats_get": (None, None), "rtb_frame_alloc_shared": (None, 0, None, None),
+        "rtb_frame_free_shared": (None, None), "rtb_frame_open_shared": (None, None, None), "rtb_frame_close_shared": (None, None),
+        "rtb_push_bands": (None, None, None, 0, 0, 0, 1, None), "rtb_debug_math": (None, 0, None, None, 0),
+    }
+    for name, args in calls.items():
+        assert getattr(L, name)(*args) == -1, name
+        assert name.encode() in L.rtb_last_error(), (name, L.rtb_last_error())
+    L.rtb_context_destroy(None)                                   # a no-op, like free(NULL)
+    assert rtb.lib().rtb_context_create(0, None) == -1
+
+
 def test_cpp_dropin_builds():
     """The C++ classes with the reference's names compile and link against the C-ABI (kernel.cu-style demo)."""
     cpp = os.path.join(ROOT, "cuda_raytracing_b200", "cpp")
