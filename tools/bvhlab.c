@@ -156,6 +156,7 @@ static int collapse(int bid, int width)
 }
 
 // ------------------------------------------------------------------ traversal (closest hit), counting
+static int g_last_tri = -1;
 static int tri_hit(int t, const float* o, const float* d, float* tmax)
 {
     const float* v = g_tri + 9 * t;
@@ -172,19 +173,22 @@ static int tri_hit(int t, const float* o, const float* d, float* tmax)
     float t_ = (e2[0] * q[0] + e2[1] * q[1] + e2[2] * q[2]) * inv;
     if (t_ <= 0 || t_ >= *tmax) return 0;
     *tmax = t_;
+    g_last_tri = t;
     return 1;
 }
 
 typedef struct { float t; int ref; } SE;
 
-// rays: n x 6 (origin, direction).  out: per ray [nodes, tris, hit]
-void lab_trace(const float* rays, int n, int32_t* out)
+// rays: n x 6 (origin, direction).  out: per ray [nodes, tris, hit].  tio (optional): per ray [tmax in / closest t out, hit triangle
+// or -1 (as a float)] so that a caller can chain several instances of the mesh along one ray
+void lab_trace_t(const float* rays, int n, int32_t* out, float* tio)
 {
     SE stack[256];
     for (int r = 0; r < n; r++) {
         const float* o = rays + 6 * r; const float* d = o + 3;
         float id[3]; for (int a = 0; a < 3; a++) id[a] = 1.0f / (fabsf(d[a]) < 1e-20f ? 1e-20f : d[a]);
-        float tmax = FLT_MAX; int sp = 0, nodes = 0, tris = 0, hit = 0;
+        float tmax = tio ? tio[2 * r] : FLT_MAX; int sp = 0, nodes = 0, tris = 0, hit = 0;
+        g_last_tri = -1;
         int cur = 0;
         for (;;) {
             if (cur >= 0) {
@@ -213,8 +217,10 @@ void lab_trace(const float* rays, int n, int32_t* out)
             if (!got) break;
         }
         out[3 * r] = nodes; out[3 * r + 1] = tris; out[3 * r + 2] = hit;
+        if (tio) { tio[2 * r] = tmax; tio[2 * r + 1] = (float)g_last_tri; }
     }
 }
+void lab_trace(const float* rays, int n, int32_t* out) { lab_trace_t(rays, n, out, 0); }
 
 // builder: 0 = Morton LBVH (bits per axis), 1 = binned SAH.  Returns the wide-node count; stats[0] = leaves, stats[1] = SAH cost of the root
 int lab_build(const float* tris, int n, int builder, int bits, int max_leaf, int width, float* stats)
