@@ -27,7 +27,10 @@ rays = np.ascontiguousarray(np.concatenate([org, d], axis=1), np.float32)
 print("mesh %d triangles, %d rays through its box" % (len(tris), R))
 print("%-22s %5s %9s %8s | %14s %14s | %14s %14s" % ("builder", "width", "nodes", "leaves", "hit: nodes", "tris", "miss: nodes", "tris"))
 ref = None
-for name, builder, bits in (("LBVH 10 bits/axis", 0, 10), ("LBVH 16 bits/axis", 0, 16), ("binned SAH (16 bins)", 1, 0)):
+L.lab_set_quant.argtypes = [C.c_int]
+for name, builder, bits, quant in (("LBVH 10 bits/axis", 0, 10, 0), ("LBVH 16 bits/axis", 0, 16, 0), ("binned SAH (16 bins)", 1, 0, 0),
+                                   ("LBVH, 8-bit child boxes", 0, 10, 8), ("LBVH, 6-bit child boxes", 0, 10, 6)):
+    L.lab_set_quant(quant)
     for width in (4, 8):
         stats = np.zeros(2, np.float32)
         t0 = time.time()

@@ -133,6 +133,26 @@ static void fit(int id, int max_leaf)
     nd->cost = nd->leaf ? c_leaf : c_split;
 }
 
+static int g_quant_bits = 0;     // > 0: child boxes snapped outwards to a 2^bits grid on the node's own box (power-of-two cell size per axis,
+                                 // as in compressed wide BVHs), to count what quantised nodes cost in extra visits
+void lab_set_quant(int bits) { g_quant_bits = bits; }
+
+static void quantise(WNode* w)
+{
+    Box nb; box_init(&nb);
+    for (int k = 0; k < w->n; k++) box_merge(&nb, &w->cb[k]);
+    const float cells = (float)((1 << g_quant_bits) - 1);
+    for (int a = 0; a < 3; a++) {
+        float ext = nb.hi[a] - nb.lo[a];
+        if (!(ext > 0)) continue;
+        float cell = exp2f(ceilf(log2f(ext / cells)));
+        for (int k = 0; k < w->n; k++) {
+            w->cb[k].lo[a] = nb.lo[a] + floorf((w->cb[k].lo[a] - nb.lo[a]) / cell) * cell;
+            w->cb[k].hi[a] = nb.lo[a] + ceilf((w->cb[k].hi[a] - nb.lo[a]) / cell) * cell;
+        }
+    }
+}
+
 static int collapse(int bid, int width)
 {
     int wid = g_nw++;
@@ -152,6 +172,7 @@ static int collapse(int bid, int width)
         if (g_b[slot[k]].leaf) g_w[wid].ref[k] = ~((g_b[slot[k]].first << 4) | (g_b[slot[k]].count - 1));
         else { int c = collapse(slot[k], width); g_w[wid].ref[k] = c; }
     }
+    if (g_quant_bits > 0) quantise(&g_w[wid]);
     return wid;
 }
 
