@@ -150,6 +150,19 @@ struct TraceState {
                 else if (cur < T.n_blas && nodes == T.g_blas) np = T.s_blas + cur * NODE_F4;
             }
             test_node<SMEM>(np, r, tmax, k, refs);
+#ifdef RTB_NEAREST_ONLY
+            // A/B variant, measured SLOWER and therefore off (C3 8.17 -> 8.57 ms, same image; profiles/r01f_ab_experiments.txt): only
+            // the nearest child is singled out; the other hit children are pushed in SLOT order -- no sorting network, no ref
+            // selects for them (tools/bvh_lab.py: +3.5 % node visits for hitting rays).  Every entry carries its own entry
+            // distance, so the pop still culls.
+            const unsigned kmin = min(min(k[0], k[1]), min(k[2], k[3]));      // keys are distinct (slot in the low bits) unless all miss
+            if (k[0] != kmin && k[0] != 0xffffffffu) stk.put(sp++, make_uint2(k[0] & ~3u, (unsigned)refs.x));
+            if (k[1] != kmin && k[1] != 0xffffffffu) stk.put(sp++, make_uint2(k[1] & ~3u, (unsigned)refs.y));
+            if (k[2] != kmin && k[2] != 0xffffffffu) stk.put(sp++, make_uint2(k[2] & ~3u, (unsigned)refs.z));
+            if (k[3] != kmin && k[3] != 0xffffffffu) stk.put(sp++, make_uint2(k[3] & ~3u, (unsigned)refs.w));
+            int nxt = sel4(kmin & 3u, refs);
+            if (kmin == 0xffffffffu) nxt = pop(stk);
+#else
             RTB_CSWAP(k[0], k[1]); RTB_CSWAP(k[2], k[3]); RTB_CSWAP(k[0], k[2]); RTB_CSWAP(k[1], k[3]); RTB_CSWAP(k[1], k[2]);
             const int c0 = sel4(k[0] & 3u, refs), c1 = sel4(k[1] & 3u, refs), c2 = sel4(k[2] & 3u, refs), c3 = sel4(k[3] & 3u, refs);
             // far first, so the nearer children are popped first (misses sort last: key 0xffffffff)
@@ -158,6 +171,7 @@ struct TraceState {
             if (k[1] != 0xffffffffu) stk.put(sp++, make_uint2(k[1] & ~3u, (unsigned)c1));
             int nxt = c0;
             if (k[0] == 0xffffffffu) nxt = pop(stk);
+#endif
             if (in_blas && pend == EMPTY_REF && is_leaf_ref(nxt)) { pend = nxt; nxt = pop(stk); }
             cur = nxt;
             if (__popc(__ballot_sync(__activemask(), pend == EMPTY_REF)) <= sc.spec_thr) break;

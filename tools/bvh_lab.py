@@ -28,9 +28,12 @@ print("mesh %d triangles, %d rays through its box" % (len(tris), R))
 print("%-22s %5s %9s %8s | %14s %14s | %14s %14s" % ("builder", "width", "nodes", "leaves", "hit: nodes", "tris", "miss: nodes", "tris"))
 ref = None
 L.lab_set_quant.argtypes = [C.c_int]
-for name, builder, bits, quant in (("LBVH 10 bits/axis", 0, 10, 0), ("LBVH 16 bits/axis", 0, 16, 0), ("binned SAH (16 bins)", 1, 0, 0),
-                                   ("LBVH, 8-bit child boxes", 0, 10, 8), ("LBVH, 6-bit child boxes", 0, 10, 6)):
+L.lab_set_order.argtypes = [C.c_int]
+for name, builder, bits, quant, order in (("LBVH 10 bits/axis", 0, 10, 0, 0), ("LBVH 16 bits/axis", 0, 16, 0, 0), ("binned SAH (16 bins)", 1, 0, 0, 0),
+                                          ("LBVH, 8-bit child boxes", 0, 10, 8, 0), ("LBVH, 6-bit child boxes", 0, 10, 6, 0),
+                                          ("LBVH, nearest-first only", 0, 10, 0, 1), ("LBVH, slot order", 0, 10, 0, 2)):
     L.lab_set_quant(quant)
+    L.lab_set_order(order)
     for width in (4, 8):
         stats = np.zeros(2, np.float32)
         t0 = time.time()

@@ -199,6 +199,9 @@ static int tri_hit(int t, const float* o, const float* d, float* tmax)
 }
 
 typedef struct { float t; int ref; } SE;
+static int g_order_mode = 0;     // 0: hit children fully sorted by entry distance (the device's 5-comparator network); 1: only the nearest is
+                                 // picked, the others are pushed in slot order; 2: no ordering at all (slot order)
+void lab_set_order(int mode) { g_order_mode = mode; }
 
 // rays: n x 6 (origin, direction).  out: per ray [nodes, tris, hit].  tio (optional): per ray [tmax in / closest t out, hit triangle
 // or -1 (as a float)] so that a caller can chain several instances of the mesh along one ray
@@ -226,7 +229,8 @@ void lab_trace_t(const float* rays, int n, int32_t* out, float* tio)
                     }
                     if (tn <= tf) { h[nh].t = tn; h[nh].ref = w->ref[k]; nh++; }
                 }
-                for (int i = 1; i < nh; i++) { SE x = h[i]; int j = i - 1; while (j >= 0 && h[j].t > x.t) { h[j + 1] = h[j]; j--; } h[j + 1] = x; }
+                if (g_order_mode == 0) { for (int i = 1; i < nh; i++) { SE x = h[i]; int j = i - 1; while (j >= 0 && h[j].t > x.t) { h[j + 1] = h[j]; j--; } h[j + 1] = x; } }
+                else if (g_order_mode == 1) { int m = 0; for (int i = 1; i < nh; i++) if (h[i].t < h[m].t) m = i; if (nh) { SE x = h[m]; h[m] = h[0]; h[0] = x; } }
                 for (int i = nh - 1; i >= 1; i--) stack[sp++] = h[i];
                 if (nh) { cur = h[0].ref; continue; }
             } else {
