@@ -335,7 +335,10 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
 //   * once every tile is claimed nothing is enqueued any more (the frame tail is latency-bound: a queue hop only delays
 //     the chain); a warp leaves when no tile is unclaimed and every ring is empty.  A ray enqueued concurrently with that
 //     check is never stranded: its producer passes through the fetch path right after the enqueue and finds it.
-constexpr int QR_RINGS = 128;
+#ifndef RTB_QR_RINGS
+#define RTB_QR_RINGS 128
+#endif
+constexpr int QR_RINGS = RTB_QR_RINGS;
 constexpr int QR_CTL = 64;                      // unsigned words per ring control block: [0] head, [32] tail (separate lines)
 struct QRing {
     float4* org;                    // [QR_RINGS][cap] (origin, pixel slot)
