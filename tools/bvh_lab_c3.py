@@ -55,15 +55,15 @@ cp, sp_ = math.cos(pitch), math.sin(pitch)
 d = np.stack([d[:, 0], cp * d[:, 1] - sp_ * d[:, 2], sp_ * d[:, 1] + cp * d[:, 2]], -1)
 o = np.tile(cam, (len(d), 1))
 
-def trace(o, d):
-    """closest hit over all instances, front to back; returns t, normal, and the visit split"""
+def trace(o, d, prev):
+    """closest hit over all instances, front to back; returns t, normal, and the visit split (prev = instance a ray starts on, -1 = camera)"""
     n = len(o)
     inv = 1.0 / np.where(np.abs(d) < 1e-20, 1e-20, d)
     t0 = (wlo[None] - o[:, None]) * inv[:, None]; t1 = (whi[None] - o[:, None]) * inv[:, None]
     tn = np.minimum(t0, t1).max(2).clip(min=0); tf = np.maximum(t0, t1).min(2)
     crossed = tn <= tf                                               # n x 100
     best = np.full(n, np.inf); bn = np.zeros((n, 3)); binst = np.full(n, -1)
-    visits_hit = np.zeros(n); visits_miss = np.zeros(n); entries = np.zeros(n); tri_tests = np.zeros(n)
+    visits_hit = np.zeros(n); visits_miss = np.zeros(n); visits_self = np.zeros(n); entries = np.zeros(n); tri_tests = np.zeros(n)
     order = np.argsort(np.where(crossed, tn, np.inf), axis=1)
     for rank in range(100):
         inst = order[:, rank]
@@ -82,19 +82,21 @@ def trace(o, d):
             L.lab_trace_t(rays.ctypes.data, len(sel), out.ctypes.data, tio.ctypes.data)
             h = out[:, 2] > 0
             entries[sel] += 1; tri_tests[sel] += out[:, 1]
-            visits_hit[sel[h]] += out[h, 0]; visits_miss[sel[~h]] += out[~h, 0]
+            own = prev[sel] == i
+            visits_hit[sel[h]] += out[h, 0]; visits_miss[sel[~h & ~own]] += out[~h & ~own, 0]; visits_self[sel[~h & own]] += out[~h & own, 0]
             best[sel[h]] = tio[h, 0]; binst[sel[h]] = i
             bn[sel[h]] = nrm[tio[h, 1].astype(int)] @ R                # mesh normal -> world: R^T n
-    return best, bn, binst, visits_hit, visits_miss, entries, tri_tests, crossed.sum(1)
+    return best, bn, binst, visits_hit, visits_miss, visits_self, entries, tri_tests, crossed.sum(1)
 
 print("C3 on the host: %d triangles/BLAS, %d-wide nodes, instance boxes: %s, %dx%d pixels" % (len(tris), WIDTH, BOXES, W, H))
-print("%-10s %9s %7s | %9s %12s %12s %9s %9s" % ("bounce", "rays", "hit %", "boxes/ray", "visits: hit", "near miss", "entries", "tris"))
-tot = np.zeros(5); nrays = 0
+print("%-10s %9s %7s | %9s %12s %12s %12s %9s %9s" % ("bounce", "rays", "hit %", "boxes/ray", "visits: hit", "own inst.", "other miss", "entries", "tris"))
+tot = np.zeros(6); nrays = 0
+prev = np.full(len(o), -1)
 for depth in range(5):
-    t, nw, inst, vh, vm, ent, tt, nb = trace(o, d)
+    t, nw, inst, vh, vm, vs, ent, tt, nb = trace(o, d, prev)
     n = len(o)
-    print("%-10d %9d %7.1f | %9.2f %12.2f %12.2f %9.2f %9.2f" % (depth, n, 100 * np.isfinite(t).mean(), nb.mean(), vh.mean(), vm.mean(), ent.mean(), tt.mean()), flush=True)
-    tot += np.array([vh.sum(), vm.sum(), ent.sum(), tt.sum(), nb.sum()]); nrays += n
+    print("%-10d %9d %7.1f | %9.2f %12.2f %12.2f %12.2f %9.2f %9.2f" % (depth, n, 100 * np.isfinite(t).mean(), nb.mean(), vh.mean(), vs.mean(), vm.mean(), ent.mean(), tt.mean()), flush=True)
+    tot += np.array([vh.sum(), vs.sum(), vm.sum(), ent.sum(), tt.sum(), nb.sum()]); nrays += n
     hit = np.isfinite(t)
     if not hit.any():
         break
@@ -104,5 +106,6 @@ for depth in range(5):
     nn = np.where((dd * nn).sum(1, keepdims=True) > 0, -nn, nn)
     d = dd - 2 * (dd * nn).sum(1, keepdims=True) * nn
     o = p + 1e-4 * nn
-print("all closest-hit rays: %.2f BLAS visits per ray in instances that are hit, %.2f in near misses, %.2f instance entries, %.2f triangle tests, %.2f boxes crossed"
-      % tuple(tot / nrays))
+    prev = inst[hit]
+print("all closest-hit rays: %.2f BLAS visits per ray in instances that are hit, %.2f leaving the instance the ray starts on, %.2f in other instances it misses, "
+      "%.2f instance entries, %.2f triangle tests, %.2f boxes crossed" % tuple(tot / nrays))
