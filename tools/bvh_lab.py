@@ -31,7 +31,8 @@ L.lab_set_quant.argtypes = [C.c_int]
 L.lab_set_order.argtypes = [C.c_int]
 for name, builder, bits, quant, order in (("LBVH 10 bits/axis", 0, 10, 0, 0), ("LBVH 16 bits/axis", 0, 16, 0, 0), ("binned SAH (16 bins)", 1, 0, 0, 0),
                                           ("LBVH, 8-bit child boxes", 0, 10, 8, 0), ("LBVH, 6-bit child boxes", 0, 10, 6, 0),
-                                          ("LBVH, nearest-first only", 0, 10, 0, 1), ("LBVH, slot order", 0, 10, 0, 2)):
+                                          ("LBVH, nearest-first only", 0, 10, 0, 1), ("LBVH, slot order", 0, 10, 0, 2),
+                                          ("LBVH, octant-diagonal order", 0, 10, 0, 3), ("LBVH, 8-bit + octant order", 0, 10, 8, 3)):
     L.lab_set_quant(quant)
     L.lab_set_order(order)
     for width in (4, 8):

@@ -230,6 +230,14 @@ void lab_trace_t(const float* rays, int n, int32_t* out, float* tio)
                     if (tn <= tf) { h[nh].t = tn; h[nh].ref = w->ref[k]; nh++; }
                 }
                 if (g_order_mode == 0) { for (int i = 1; i < nh; i++) { SE x = h[i]; int j = i - 1; while (j >= 0 && h[j].t > x.t) { h[j + 1] = h[j]; j--; } h[j + 1] = x; } }
+                else if (g_order_mode == 3) {          // by the child centre projected on the ray's octant diagonal: the best an octant-indexed, sort-free order can do
+                    float key[8];
+                    for (int i = 0; i < nh; i++) {
+                        int k = -1; for (int q = 0; q < w->n; q++) if (w->ref[q] == h[i].ref) k = q;
+                        key[i] = 0; for (int a = 0; a < 3; a++) key[i] += (w->cb[k].lo[a] + w->cb[k].hi[a]) * (d[a] < 0 ? -1.f : 1.f);
+                    }
+                    for (int i = 1; i < nh; i++) { SE x = h[i]; float kx = key[i]; int j = i - 1; while (j >= 0 && key[j] > kx) { h[j + 1] = h[j]; key[j + 1] = key[j]; j--; } h[j + 1] = x; key[j + 1] = kx; }
+                }
                 else if (g_order_mode == 1) { int m = 0; for (int i = 1; i < nh; i++) if (h[i].t < h[m].t) m = i; if (nh) { SE x = h[m]; h[m] = h[0]; h[0] = x; } }
                 for (int i = nh - 1; i >= 1; i--) stack[sp++] = h[i];
                 if (nh) { cur = h[0].ref; continue; }
