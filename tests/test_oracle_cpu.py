@@ -393,3 +393,13 @@ def test_headless_presentation_script_overlay_png(oracle, tmp_path):
     ys, xs = np.nonzero(overlay)
     assert ys.min() >= 9 and ys.max() <= 29 and xs.min() >= 10 and xs.max() < 10 + 18 * len("FPS: 12.500000")
     assert overlay[9:30, 10:25].all(axis=1)[0]                                   # top bar of the 'F'
+
+
+def test_node8_quantisation_is_conservative(tmp_path):
+    """Groundwork for the 8-wide quantised node (not on the product path yet): the encoder of rtb_node8.cuh must
+    produce boxes that, decoded with the tracer's one-fma arithmetic, contain the exact child boxes -- for every magnitude,
+    flat and point boxes included -- and stay within two cells of them."""
+    exe = str(tmp_path / "node8_check")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-o", exe, os.path.join(ROOT, "tests", "node8_check.cpp")])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.startswith("ok:"), r.stdout + r.stderr
