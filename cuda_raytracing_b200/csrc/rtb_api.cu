@@ -4,6 +4,7 @@
 #include "rtb_build.cuh"
 #include "rtb_render.cuh"
 #include "rtb_hostmath.h"
+#include "rtb_cwnode.cuh"
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -63,7 +64,7 @@ struct rtb_context {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
     int last_launches = 0;
-    int opt_counters = 0, opt_leaf = 8, opt_key_bits = 0;
+    int opt_counters = 0, opt_leaf = MAX_LEAF, opt_key_bits = 0;
     void* wf = nullptr;            // wavefront state (rtb_wavefront.cu)
 };
 
@@ -186,7 +187,7 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
     m.n = n; m.alive = true;
     rtb_mesh_info& I = m.info;
     I.num_triangles = n; I.num_nodes = m.bvh.num_nodes; I.num_leaves = m.bvh.num_leaves; I.max_leaf_size = m.bvh.max_leaf;
-    I.depth = m.bvh.depth; I.stack_need = 3 * m.bvh.depth + 2; I.build_ms = ms; I.sah_cost = m.bvh.sah;
+    I.depth = m.bvh.depth; I.stack_need = m.bvh.depth + 1; I.build_ms = ms; I.sah_cost = m.bvh.sah;
     for (int k = 0; k < 3; k++) { I.bounds_min[k] = m.bvh.bounds[k]; I.bounds_max[k] = m.bvh.bounds[k + 3]; }
     I.device_bytes = sizeof(float4) * TRI_F4 * nn + sizeof(float2) * 3 * nn + sizeof(float4) * NODE_F4 * (size_t)m.bvh.node_cap +
                      sizeof(unsigned) * (size_t)m.bvh.order_cap;
@@ -311,19 +312,19 @@ static int mesh_cut(rtb_context* c, MeshRec& m, int budget)
         }
         for (int k = 0; k < 3; k++) m.cut.push_back(b[k + 3] + (b[k] - m.cut[k]));
     } else if (m.n > 0 && finite && budget > 1 && m.bvh.num_nodes >= 1) {
-        const int K = std::min(m.bvh.num_nodes, 85);
+        const int K = std::min(m.bvh.num_nodes, 73);                  // the root and its first two levels at most
         std::vector<float4> nd((size_t)K * NODE_F4);
         CU(cudaMemcpy(nd.data(), m.bvh.nodes, sizeof(float4) * nd.size(), cudaMemcpyDeviceToHost), "read top BLAS levels");
-        struct Box { float lo[3], hi[3]; int ref; };
+        struct Box { float lo[3], hi[3]; int node; };     // node >= 0: an inner child that may be opened further
         std::vector<Box> open, done;                      // open: FIFO (head index), so the cut is opened level by level
         auto children = [&](int node) {
-            const float* f = (const float*)&nd[(size_t)node * NODE_F4];
-            for (int k = 0; k < 4; k++) {
-                int ref; memcpy(&ref, f + 24 + k, 4);
-                if (ref == EMPTY_REF) continue;
+            const CwNodeView v = cw_view(&nd[(size_t)node * NODE_F4]);
+            for (int k = 0; k < 8; k++) {
+                const int kind = cw_child_kind(v, k);
+                if (kind == 0) continue;
                 Box x;
-                for (int a = 0; a < 3; a++) { x.lo[a] = f[8 * a + k]; x.hi[a] = f[8 * a + 4 + k]; }
-                x.ref = ref;
+                cw_child_box(v, k, x.lo, x.hi);           // the decoded (quantised, hence conservative) child box
+                x.node = kind == 1 ? cw_child_node(v, k) : -1;
                 open.push_back(x);
             }
         };
@@ -331,7 +332,7 @@ static int mesh_cut(rtb_context* c, MeshRec& m, int budget)
         size_t head = 0;
         while (head < open.size()) {
             const Box x = open[head++];
-            if (x.ref >= 0 && x.ref < K && done.size() + (open.size() - head) + 4 <= (size_t)budget) children(x.ref);
+            if (x.node >= 0 && x.node < K && done.size() + (open.size() - head) + 8 <= (size_t)budget) children(x.node);
             else done.push_back(x);
         }
         for (const Box& x : done)
@@ -469,6 +470,16 @@ static int make_scene(rtb_context* c, SceneDev& sc)
     for (const auto& in : c->instances_h)
         if (!c->meshes[in.mesh_index].alive) return fail(RTB_ERR_STATE, "render: an instance refers to a destroyed mesh");
     if (c->tlas_dirty) { int rc = rebuild_tlas(c, (int)c->instances_h.size()); if (rc != RTB_OK) return rc; }   // stale boxes only
+    // Worst-case traversal stack: one group per TLAS level, the sentinel, one group per level of the deepest BLAS in use.
+    // A scene that needs more than the kernels' fixed stack is refused here, never rendered wrong.
+    {
+        int deepest = 0;
+        for (const auto& in : c->instances_h) deepest = std::max(deepest, c->meshes[in.mesh_index].bvh.depth);
+        const int need = (c->instances_h.size() > 1 ? c->tlas.depth + 1 : 0) + deepest + 1;
+        if (need > STACK_CAP)
+            return fail(RTB_ERR_OVERFLOW, "render: the scene's trees need a traversal stack of " + std::to_string(need) + " entries, the kernels have " +
+                                              std::to_string((int)STACK_CAP) + " (a degenerate mesh: many primitives with one centroid?)");
+    }
     if (c->mesh_table_dirty) {
         const int n = (int)c->meshes.size(), cap = std::max(n, 1);
         if (c->meshes_cap < cap) {

@@ -245,6 +245,7 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
     TopLevels T;
     T.n_tlas = T.n_blas = 0; T.s_tlas = T.s_blas = T.g_blas = nullptr;
     if (SMEM) stage_top_levels(sc, s_top, T);
+    init_pick_lut();
     RTB_DECL_STACK(stk);
     TraceState S;
     MegaSink sink;
@@ -374,6 +375,7 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
     const f3 L = mk3(P.light_dir.x, P.light_dir.y, P.light_dir.z);
     TopLevels T;
     T.n_tlas = T.n_blas = 0; T.s_tlas = T.s_blas = T.g_blas = nullptr;
+    init_pick_lut();
     RTB_DECL_STACK(stk);
     TraceState S;
     MegaSink sink;

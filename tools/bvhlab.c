@@ -153,6 +153,36 @@ static void quantise(WNode* w)
     }
 }
 
+// Compressed-wide-BVH child placement (Ylitie et al. 2017): child c goes to the slot s whose octant direction (sign bits of s)
+// best matches (centre_c - node centre); greedy on the 8 x 8 cost table.  Traversal order for a ray of octant o = slots by
+// descending (s ^ o'), no sort.  Empty slots get ref = EMPTY.
+#define EMPTY_SLOT ((int)0x80000000)
+static int g_slot_assign = 0;
+void lab_set_slots(int on) { g_slot_assign = on; }
+static void assign_slots(WNode* w)
+{
+    Box nb; box_init(&nb);
+    for (int k = 0; k < w->n; k++) box_merge(&nb, &w->cb[k]);
+    float cost[8][8]; int used_c[8] = {0}, used_s[8] = {0};
+    for (int c = 0; c < w->n; c++) for (int s = 0; s < 8; s++) {
+        float v = 0;
+        for (int a = 0; a < 3; a++) {
+            float rel = (w->cb[c].lo[a] + w->cb[c].hi[a]) - (nb.lo[a] + nb.hi[a]);
+            v += ((s >> a) & 1) ? rel : -rel;          /* slot bit a set = child on the + side of axis a */
+        }
+        cost[c][s] = v;
+    }
+    Box cb[8]; int ref[8];
+    for (int s = 0; s < 8; s++) { ref[s] = EMPTY_SLOT; box_init(&cb[s]); }
+    for (int it = 0; it < w->n; it++) {
+        int bc = -1, bs = -1; float bv = -FLT_MAX;
+        for (int c = 0; c < w->n; c++) if (!used_c[c]) for (int s = 0; s < 8; s++) if (!used_s[s] && cost[c][s] > bv) { bv = cost[c][s]; bc = c; bs = s; }
+        used_c[bc] = used_s[bs] = 1; cb[bs] = w->cb[bc]; ref[bs] = w->ref[bc];
+    }
+    for (int s = 0; s < 8; s++) { w->cb[s] = cb[s]; w->ref[s] = ref[s]; }
+    w->n = 8;
+}
+
 static int collapse(int bid, int width)
 {
     int wid = g_nw++;
@@ -173,6 +203,7 @@ static int collapse(int bid, int width)
         else { int c = collapse(slot[k], width); g_w[wid].ref[k] = c; }
     }
     if (g_quant_bits > 0) quantise(&g_w[wid]);
+    if (g_slot_assign) assign_slots(&g_w[wid]);
     return wid;
 }
 
@@ -254,6 +285,61 @@ void lab_trace_t(const float* rays, int n, int32_t* out, float* tio)
     }
 }
 void lab_trace(const float* rays, int n, int32_t* out) { lab_trace_t(rays, n, out, 0); }
+
+// Compressed-wide-BVH traversal: children visited in (slot ^ octant) order, the stack holds GROUPS (node, mask of children still
+// to visit) and cannot cull on pop (cull = 1: per-child entry distances kept, to measure what that costs); triangle leaves of a
+// node are tested right after the node (postpone = 0) .  out as lab_trace_t.
+void lab_trace_cw(const float* rays, int n, int32_t* out, float* tio, int cull)
+{
+    typedef struct { int node; unsigned mask; float tn[8]; } GE;
+    static GE stack[256];
+    for (int r = 0; r < n; r++) {
+        const float* o = rays + 6 * r; const float* d = o + 3;
+        float id[3]; for (int a = 0; a < 3; a++) id[a] = 1.0f / (fabsf(d[a]) < 1e-20f ? 1e-20f : d[a]);
+        int oct = (d[0] < 0 ? 1 : 0) | (d[1] < 0 ? 2 : 0) | (d[2] < 0 ? 4 : 0);     /* slots with bit set = + side: visited first when d < 0 ... */
+        float tmax = tio ? tio[2 * r] : FLT_MAX; int sp = 0, nodes = 0, tris = 0, hit = 0;
+        g_last_tri = -1;
+        int cur = 0;
+        for (;;) {
+            const WNode* w = &g_w[cur];
+            nodes++;
+            GE g; g.node = cur; g.mask = 0;
+            unsigned leafmask = 0;
+            for (int k = 0; k < 8; k++) {
+                if (w->ref[k] == EMPTY_SLOT) continue;
+                float tn = 0, tf = tmax;
+                for (int a = 0; a < 3; a++) {
+                    float t0 = (w->cb[k].lo[a] - o[a]) * id[a], t1 = (w->cb[k].hi[a] - o[a]) * id[a];
+                    if (t0 > t1) { float t = t0; t0 = t1; t1 = t; }
+                    if (t0 > tn) tn = t0;
+                    if (t1 < tf) tf = t1;
+                }
+                if (tn <= tf) { if (w->ref[k] >= 0) { g.mask |= 1u << k; g.tn[k] = tn; } else leafmask |= 1u << k; }
+            }
+            /* leaves of this node first, in traversal order (nearest slots first) */
+            for (int p = 0; p < 8; p++) {
+                int k = p ^ oct;                           /* priority p = 0 first: slot whose sign bits equal the ray's negative bits -> - side for + dirs */
+                if (!((leafmask >> k) & 1)) continue;
+                unsigned b = ~(unsigned)w->ref[k]; int first = (int)(b >> 4), count = (int)(b & 15u) + 1;
+                for (int i = 0; i < count; i++) { tris++; hit |= tri_hit(g_order[first + i], o, d, &tmax); }
+            }
+            int got = 0;
+            for (;;) {
+                if (g.mask == 0) { if (sp == 0) break; g = stack[--sp]; }
+                int k = -1;
+                for (int p = 0; p < 8; p++) { int q = p ^ oct; if ((g.mask >> q) & 1) { k = q; break; } }
+                g.mask &= ~(1u << k);
+                if (cull && !(g.tn[k] < tmax)) continue;
+                cur = g_w[g.node].ref[k];
+                if (g.mask) stack[sp++] = g;
+                got = 1; break;
+            }
+            if (!got) break;
+        }
+        out[3 * r] = nodes; out[3 * r + 1] = tris; out[3 * r + 2] = hit;
+        if (tio) { tio[2 * r] = tmax; tio[2 * r + 1] = (float)g_last_tri; }
+    }
+}
 
 // builder: 0 = Morton LBVH (bits per axis), 1 = binned SAH.  Returns the wide-node count; stats[0] = leaves, stats[1] = SAH cost of the root
 int lab_build(const float* tris, int n, int builder, int bits, int max_leaf, int width, float* stats)

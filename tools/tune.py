@@ -52,9 +52,18 @@ def main():
         h = int(frame.to(torch.int64).sum().item())
         if ref is None:
             ref = h
-        rays = scene.frame_stats()["rays"]
+        st = scene.frame_stats()
+        rays = st["rays"]
+        extra = {}
+        if os.environ.get("COUNT"):                          # COUNT=1: one more frame with the device counters on (slower kernel variant)
+            scene.set_option("counters", 1)
+            cam.render_scene(scene, frame.data_ptr(), W * 3)
+            torch.cuda.synchronize()
+            c = scene.frame_stats()
+            extra = dict(nodes_per_ray=round(c["nodes"] / max(1, c["rays"]), 2), tris_per_ray=round(c["tris"] / max(1, c["rays"]), 2))
+            scene.set_option("counters", 0)
         print(json.dumps(dict(config=name, knobs=dict(zip([k for k, _ in knobs], combo)), ms=round(float(np.mean(ms)), 3), ms_min=round(min(ms), 3),
-                              mrays=round(rays / np.mean(ms) / 1e3, 1), same_image=(h == ref), hash=h)), flush=True)
+                              mrays=round(rays / np.mean(ms) / 1e3, 1), same_image=(h == ref), hash=h, **extra)), flush=True)
     scene.close()
 
 if __name__ == "__main__":
