@@ -74,6 +74,18 @@ def scene_instances(cfg):
     return [(0, i % 2, p, (1.0, 1.0, 1.0)) for i, p in enumerate(poses)]
 
 
+def config_dict(cfg, name, n_tris):
+    """The workload description both arms print verbatim (the driver compares the two `config` objects)."""
+    return dict(workload=cfg["desc"], config=name, width=cfg["w"], height=cfg["h"], triangles=int(n_tris),
+                instances=len(scene_instances(cfg)), mode=cfg["mode"], max_depth=cfg["depth"], spp=cfg["spp"])
+
+
+def flops_per_ray(nodes, tris):
+    """SURVEY 8(d)'s arithmetic model restated for the 8-wide compressed node: per node visit 8 children x (6 fma + 4 min/max +
+    3 differences = 19 flops) + 18 for the per-node ray constants; per triangle test 30; 80 per ray for setup and the accept rule."""
+    return nodes * (8 * 19 + 18) + tris * 30 + 80
+
+
 class ClockSampler(threading.Thread):
     """SM clock, max clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe), through NVML
     every ~2 ms so that even a sub-millisecond-per-step config is covered; nvidia-smi -lms is the fallback."""
@@ -136,10 +148,12 @@ class ClockSampler(threading.Thread):
 
 
 def load_peaks():
+    """(HBM GB/s, SM max MHz, kind): the driver-written measured peaks, else the profiling recipe's fallback."""
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
-        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
-    return 6650.0, "fallback"
+        j = json.load(open(p))
+        return j.get("hbm_gbs", 6650.0), j.get("sm_max_mhz", 1965.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1965.0, "fallback (B200_PROFILING.md)"
 
 
 def build_tris(cfg, phase=0.0):
@@ -199,7 +213,7 @@ def run_reference(args, cfg, rank):
     sample = "%d centred rows of %dx%d per step (%s), %d spp" % (rows, W, H, cfg["desc"], spp)
     line = dict(impl="reference", metric="Mrays/s", value=val, unit="Mrays/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
                 ms_per_step=1e3 * tot_t / max(1, args.steps), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
-                data="synthetic", config=dict(workload=cfg["desc"], config=args.config),
+                data="synthetic", config=config_dict(cfg, args.config, len(tris)),
                 cpu_baseline=dict(value=val, unit="Mrays/s", cores=cores, kind=kind, sample=sample),
                 e2e=dict(value=val, unit="Mrays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line), flush=True)
@@ -340,44 +354,79 @@ def main():
     value = rays / (ms * 1e-3) / 1e6
     e2e_value = rays_e / (ms_e * 1e-3) / 1e6
 
-    # ---- roofline of the dominant kernel (trace+shade): algorithmic bytes from the traversal counters ----
-    peak, peak_kind = load_peaks()
+    # ---- roofline of the dominant kernel: the render launch of THIS rank's share, on the SAME frames as the timed loop ----
+    # (a) kernel time: CUDA events on the launching stream around rtb_render alone (no exchange, no copy), L2 flushed before
+    #     each frame like the timed loop; (b) work: the device counters of the same frames (a slower counting variant of the
+    #     kernel, never timed).  Every rank measures its own share; rank 0 reports its own and the min / median / max over ranks.
+    peak, sm_mhz, peak_kind = load_peaks()
     roof = None
     cpu = None
     ref_cuda = None
-    if rank == 0:
-        scene.set_option("counters", 1)
-        cam.tile_rank, cam.tile_count = 0, 1
-        cam.pose = np.array(camera_pose(cfg, args.warmup), np.float32)
-        cam.render_scene(scene, frame.data_ptr(), pitch, synchronize=True)
+    own_target = target if not (world > 1 and args.exchange == "nccl") else frame.data_ptr()
+    kt, variants = [], set()
+    for k in range(args.steps):
+        if args.config == "c5":
+            scene.rebuild_mesh(0, device_ptr=anim[(args.warmup + k) % len(anim)].data_ptr(), n=len(tris))
+        cam.pose = np.array(camera_pose(cfg, args.warmup + k), np.float32)
+        if not args.no_flush:
+            flush.fill_(k & 0xFF)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        cam.render_scene(scene, own_target, pitch, stream=C.c_void_p(stream.cuda_stream))
+        e1.record(stream)
+        torch.cuda.synchronize()
+        kt.append(e0.elapsed_time(e1))
+        variants.add(scene.frame_stats()["kernel_variant"])
+    kms = float(np.mean(kt))
+    n_count = min(args.steps, 2 if cfg["mode"] == 3 else args.steps)       # path tracing: the counting variant costs seconds per frame
+    scene.set_option("counters", 1)
+    cnt = dict(rays=0, nodes=0, tris=0)
+    for k in range(n_count):
+        cam.pose = np.array(camera_pose(cfg, args.warmup + k), np.float32)
+        cam.render_scene(scene, own_target, pitch, synchronize=True)
         st = scene.frame_stats()
-        scene.set_option("counters", 0)
-        queue_hops = max(0, st["rays"] - W * H * (cfg["spp"] if cfg["mode"] == 3 else 1)) if cfg["mode"] >= 2 else 0
-        alg_bytes = st["nodes"] * 112 + st["tris"] * 64 + W * H * 3 + queue_hops * 64
-        # time the same full frame on the same stream
-        kt = []
-        for k in range(6):                               # first launch after the counters switch is a warm-up
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            flush.fill_(k)
-            e0.record(stream)
-            cam.render_scene(scene, frame.data_ptr(), pitch, stream=C.c_void_p(stream.cuda_stream))
-            e1.record(stream)
-            torch.cuda.synchronize()
-            kt.append(e0.elapsed_time(e1))
-        kms = float(np.mean(kt[1:]))
+        for key in cnt:
+            cnt[key] += st[key]
+    scene.set_option("counters", 0)
+    barrier()
+    kall = torch.tensor([kms], dtype=torch.float64, device=dev)
+    if world > 1:
+        gathered = [torch.zeros_like(kall) for _ in range(world)]
+        dist.all_gather(gathered, kall)
+        kall = torch.cat(gathered)
+    kall = kall.cpu().numpy()
+    if rank == 0:
+        my_pixels = W * H / world
+        nodes_per_ray, tris_per_ray = cnt["nodes"] / max(1, cnt["rays"]), cnt["tris"] / max(1, cnt["rays"])
+        rays_f = cnt["rays"] / max(1, n_count)                               # rays per frame of this rank's share
+        hops = max(0.0, rays_f - my_pixels * (cfg["spp"] if cfg["mode"] == 3 else 1)) if cfg["mode"] >= 2 else 0.0
+        node_b, tri_b, hop_b = 80, 64, 64                                   # bytes per node visit / triangle test / queue hop (32 written + 32 read)
+        alg_bytes = rays_f * (nodes_per_ray * node_b + tris_per_ray * tri_b) + my_pixels * 3 + hops * hop_b
         ach = alg_bytes / (kms * 1e-3) / 1e9
-        kname = "k_megaq (fused persistent path kernel with in-kernel ray queues)" if cfg["mode"] >= 2 else "k_render_direct"
-        traffic = None                                   # dram bytes per launch of that kernel from the committed ncu --set full capture
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        flops = rays_f * flops_per_ray(nodes_per_ray, tris_per_ray)
+        fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12                      # TFLOP/s: SMs x FP32 lanes x 2 (fma) x clock
+        fp32_ach = flops / (kms * 1e-3) / 1e12
+        variant = sorted(variants)[-1] if variants else -1
+        kname = {2: "k_megaq (persistent path kernel with in-kernel ray queues)", 1: "k_mega (persistent path kernel, lane-owned chains)",
+                 0: "k_trace_queue (staged wavefront)", -1: "k_render_direct"}.get(variant, "?")
+        prof = {}
+        tp = os.path.join(ROOT, "profiles", "traffic.json")                  # per-launch numbers of the committed ncu --set full capture
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(args.config)
-        roof = dict(bound="hbm", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=traffic, peak_kind=peak_kind,
-                    kernel=kname, kernel_ms=kms, nodes_per_ray=st["nodes"] / max(1, st["rays"]),
-                    tris_per_ray=st["tris"] / max(1, st["rays"]), rays=st["rays"], alg_bytes=alg_bytes,
-                    note="algorithmic bytes = 112 B/node visit + 64 B/triangle test + 3 B/pixel (+ 64 B/queue hop, staged pipeline only); "
-                         "node and triangle fetches are mostly L1/L2 hits (BLAS ~100 MB), so the kernel is issue/latency bound, "
-                         "not HBM bound: see DESIGN.md 4 and profiles/")
-        cam.tile_rank, cam.tile_count = rank, world
+            prof = json.load(open(tp)).get(args.config) or {}
+        if not isinstance(prof, dict):
+            prof = dict(dram_bytes=prof)
+        traffic = prof.get("dram_bytes") if world == 1 else None             # the capture is of the full frame on one GPU
+        roof = dict(bound=prof.get("bound", "issue"), achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=traffic, peak_kind=peak_kind,
+                    kernel=kname, kernel_variant=variant, kernel_ms=kms, kernel_ms_ranks=dict(min=float(kall.min()), median=float(np.median(kall)), max=float(kall.max())),
+                    share_of_step=kms / (ms / args.steps), frames="the %d timed poses, L2 flushed, this rank's share (1/%d of the bands)" % (args.steps, world),
+                    ceilings=dict(hbm=dict(achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, alg_bytes=alg_bytes,
+                                           dram_frac=(traffic / (kms * 1e-3) / 1e9 / peak) if traffic else None),
+                                  fp32=dict(achieved=fp32_ach, peak=fp32_peak, unit="TFLOP/s", frac=fp32_ach / fp32_peak, flops=flops),
+                                  issue=dict(frac=prof.get("issue_active"), source=prof.get("source"))),
+                    nodes_per_ray=nodes_per_ray, tris_per_ray=tris_per_ray, rays=rays_f,
+                    note="algorithmic bytes = %d B per node visit + %d B per triangle test + 3 B per pixel + %d B per queue hop; node and triangle "
+                         "fetches are mostly L1/L2 hits (the scene is L2-sized), so neither the HBM nor the FP32 ceiling binds: the kernel is bound "
+                         "by issue slots and the latency of dependent node fetches (ncu: profiles/, DESIGN.md 4)" % (node_b, tri_b, hop_b))
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -403,21 +452,21 @@ def main():
             try:
                 sys.path.insert(0, os.path.join(ROOT, "tests"))
                 import refcuda
-                ref_cuda = refcuda.time_reference_kernel(tris, scene_materials(cfg), scene_instances(cfg), W, H, K, D, pose)
+                poses = [camera_pose(cfg, args.warmup + k) for k in range(min(args.steps, 4))]
+                ref_cuda = refcuda.time_reference_kernel(tris, scene_materials(cfg), scene_instances(cfg), W, H, K, D, poses)
             except Exception as ex:                      # the reported baseline is optional, the bench line is not
                 ref_cuda = dict(error=str(ex)[:200])
 
     if rank == 0:
         line = dict(metric="Mrays/s", value=value, unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
                     ms_per_step=ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
-                    config=dict(workload=cfg["desc"], config=args.config, width=W, height=H, triangles=int(len(tris)),
-                                instances=len(scene_instances(cfg)), mode=cfg["mode"], max_depth=cfg["depth"], spp=cfg["spp"],
-                                parallelism="image bands of %d rows interleaved over %d GPU(s), scene replicated, bands to rank 0: %s" % (
-                                    api.BAND_ROWS, world, {"direct": "kernel stores into rank 0's frame over NVLink peer memory",
-                                                           "push": "one strided peer copy per rank over NVLink", "nccl": "NCCL gather"}[args.exchange] if world > 1 else "-"),
-                                l2="flushed between steps with a 256 MiB write (untimed)" if not args.no_flush else "not flushed",
-                                rays_per_frame=rays / args.steps, blas=dict(nodes=info["num_nodes"], leaves=info["num_leaves"], depth=info["depth"],
-                                                                         build_ms=info["build_ms"], bytes=info["device_bytes"])),
+                    config=config_dict(cfg, args.config, len(tris)),
+                    details=dict(parallelism="image bands of %d rows interleaved over %d GPU(s), scene replicated, bands to rank 0: %s" % (
+                                     api.BAND_ROWS, world, {"direct": "kernel stores into rank 0's frame over NVLink peer memory",
+                                                            "push": "one strided peer copy per rank over NVLink", "nccl": "NCCL gather"}[args.exchange] if world > 1 else "-"),
+                                 l2="flushed between steps with a 256 MiB write (untimed)" if not args.no_flush else "not flushed",
+                                 rays_per_frame=rays / args.steps, blas=dict(nodes=info["num_nodes"], leaves=info["num_leaves"], depth=info["depth"],
+                                                                          build_ms=info["build_ms"], bytes=info["device_bytes"])),
                     clocks=clocks, gpu_launches=launches,
                     e2e=dict(value=e2e_value, unit="Mrays/s", h2d_bytes_per_step=int(C.sizeof(api.RenderParams)), d2h_bytes_per_step=int(H * pitch),
                              ms_per_step=ms_e / args.steps),

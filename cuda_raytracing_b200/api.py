@@ -68,7 +68,7 @@ class MeshInfo(C.Structure):
 
 class FrameStats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
-                ("device_ms", C.c_float), ("overflow", C.c_int), ("launches", C.c_int)]
+                ("device_ms", C.c_float), ("overflow", C.c_int), ("launches", C.c_int), ("kernel_variant", C.c_int)]
 
 
 assert C.sizeof(CInstance) == 104 and C.sizeof(CMaterial) == 48 and C.sizeof(Lre) == 24
@@ -336,7 +336,7 @@ class Scene:
     def frame_stats(self):
         st = FrameStats()
         _check(lib().rtb_frame_stats_get(self._ctx, C.byref(st)))
-        return dict(rays=st.rays, nodes=st.nodes_visited, tris=st.tris_tested, device_ms=st.device_ms, launches=st.launches)
+        return dict(rays=st.rays, nodes=st.nodes_visited, tris=st.tris_tested, device_ms=st.device_ms, launches=st.launches, kernel_variant=st.kernel_variant)
 
     def synchronize(self):
         _check(lib().rtb_synchronize(self._ctx))

@@ -65,6 +65,9 @@ struct rtb_context {
     float last_ms = 0.f;
     int last_launches = 0;
     int opt_counters = 0, opt_leaf = MAX_LEAF, opt_key_bits = 0;
+    rtb::Tune tune;                // kernel tuning knobs of THIS context (rtb_set_option)
+    float sah_node_cost = 1.0f;    // option "sah_node" (permille)
+    rtb::LaunchInfo last_info;
     void* wf = nullptr;            // wavefront state (rtb_wavefront.cu)
 };
 
@@ -139,17 +142,17 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     if (n == "counters") c->opt_counters = value;
     else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
     else if (n == "key_bits") c->opt_key_bits = value;
-    else if (n == "sah_node") rtb::g_sah_node_cost = 0.001f * (float)std::max(1, std::min(value, 100000));
+    else if (n == "sah_node") c->sah_node_cost = 0.001f * (float)std::max(1, std::min(value, 100000));
     else if (n == "inst_cut") { c->opt_inst_cut = std::max(1, std::min(value, 1024)); c->tlas_dirty = !c->instances_h.empty(); }
-    else if (n == "fused") rtb::g_tune.fused = value;
-    else if (n == "cost_order") rtb::g_tune.cost_order = value;
-    else if (n == "queue_keep") rtb::g_tune.queue_keep = std::max(1, std::min(value, 33));
-    else if (n == "tail_idle") rtb::g_tune.tail_idle = std::max(1, std::min(value, 32));
-    else if (n == "spec_thr") rtb::g_tune.spec_thr = std::max(0, std::min(value, 31));
-    else if (n == "smem_top") rtb::g_tune.smem_top = std::max(0, std::min(value, 341));
-    else if (n == "trace_minb") rtb::g_tune.trace_minb = value;
-    else if (n == "direct_minb") rtb::g_tune.direct_minb = value;
-    else if (n == "refill_idle") rtb::g_tune.refill_idle = std::max(1, std::min(value, 32));
+    else if (n == "fused") c->tune.fused = value;
+    else if (n == "cost_order") c->tune.cost_order = value;
+    else if (n == "queue_keep") c->tune.queue_keep = std::max(1, std::min(value, 33));
+    else if (n == "tail_idle") c->tune.tail_idle = std::max(1, std::min(value, 32));
+    else if (n == "spec_thr") c->tune.spec_thr = std::max(0, std::min(value, 31));
+    else if (n == "smem_top") c->tune.smem_top = std::max(0, std::min(value, 341));
+    else if (n == "trace_minb") c->tune.trace_minb = value;
+    else if (n == "direct_minb") c->tune.direct_minb = value;
+    else if (n == "refill_idle") c->tune.refill_idle = std::max(1, std::min(value, 32));
     else return fail(RTB_ERR_INVALID, "rtb_set_option: unknown option " + n);
     return RTB_OK;
 }
@@ -180,7 +183,7 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
     }
     CU(cudaEventRecord(c->ev0, st), "event");
     int key_bits = c->opt_key_bits ? c->opt_key_bits : (n > (1 << 21) ? 64 : 32);
-    CU(build_bvh(tris_d, bmin, bmax, n, c->opt_leaf, key_bits, m.bvh, c->ws, st, m.tri_rec, m.uvs, c->ev1), "build_bvh");
+    CU(build_bvh(tris_d, bmin, bmax, n, c->opt_leaf, key_bits, c->sah_node_cost, m.bvh, c->ws, st, m.tri_rec, m.uvs, c->ev1), "build_bvh");
     CU(cudaEventSynchronize(c->ev1), "build sync");
     float ms = 0.f;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
@@ -261,7 +264,7 @@ int rtb_mesh_destroy(rtb_context* c, int id)
 }  // extern "C"
 
 // ------------------------------------------------------------------ scene
-namespace rtb { extern int g_wave_launches; cudaError_t launch_wavefront(rtb_context* c, void** wf_state, const SceneDev& sc, const FrameParams& P, unsigned char* img,
+namespace rtb { cudaError_t launch_wavefront(const Tune& tune, LaunchInfo& info, void** wf_state, const SceneDev& sc, const FrameParams& P, unsigned char* img,
                                              size_t pitch, const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st); }
 
 extern "C" {
@@ -435,7 +438,7 @@ static int rebuild_tlas(rtb_context* c, int only)
         CU(cudaMemcpy(c->ibox_min, c->ibox_lo_h.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
         CU(cudaMemcpy(c->ibox_max, c->ibox_hi_h.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice), "boxes upload");
     }
-    CU(build_bvh(nullptr, c->ibox_min, c->ibox_max, n, 1, 32, c->tlas, c->ws, 0), "build TLAS");
+    CU(build_bvh(nullptr, c->ibox_min, c->ibox_max, n, 1, 32, c->sah_node_cost, c->tlas, c->ws, 0), "build TLAS");
     c->tlas_dirty = false;
     return RTB_OK;
 }
@@ -501,13 +504,13 @@ static int make_scene(rtb_context* c, SceneDev& sc)
     sc.tlas_extent = bounds_extent(c->tlas.bounds, sc.num_instances);
     // top tree levels to stage in shared memory (rtb_tma.cuh): the TLAS prefix and the prefix of the BLAS most instances use
     sc.top_blas = nullptr; sc.top_tlas_n = sc.top_blas_n = 0;
-    sc.spec_thr = rtb::g_tune.spec_thr;
-    if (rtb::g_tune.smem_top > 0 && !c->instances_h.empty()) {
+    sc.spec_thr = c->tune.spec_thr;
+    if (c->tune.smem_top > 0 && !c->instances_h.empty()) {
         std::vector<int> uses(c->meshes.size(), 0);
         for (const auto& in : c->instances_h) uses[in.mesh_index]++;
         const int best = (int)(std::max_element(uses.begin(), uses.end()) - uses.begin());
         const MeshRec& m = c->meshes[best];
-        if (m.bvh.nodes && m.bvh.num_nodes > 0) { sc.top_blas = m.bvh.nodes; sc.top_blas_n = std::min(m.bvh.num_nodes, rtb::g_tune.smem_top); }
+        if (m.bvh.nodes && m.bvh.num_nodes > 0) { sc.top_blas = m.bvh.nodes; sc.top_blas_n = std::min(m.bvh.num_nodes, c->tune.smem_top); }
         if (sc.num_instances > 1) sc.top_tlas_n = std::min(c->tlas.num_nodes, 48);
     }
     return RTB_OK;
@@ -541,12 +544,12 @@ static int render_impl(rtb_context* c, const rtb_render_params* p, unsigned char
     CU(cudaMemsetAsync(c->counters_d, 0, sizeof(Counters), st), "counters reset");
     if (p->mode == RTB_MODE_REFERENCE || p->mode == RTB_MODE_SHADOW)
     {
-        CU(launch_render(sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "render launch");
-        c->last_launches = 1;
+        CU(launch_render(c->tune, sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "render launch");
+        c->last_info.launches = 1; c->last_info.variant = -1;
     } else {
-        CU(launch_wavefront(c, &c->wf, sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "wavefront launch");
-        c->last_launches = g_wave_launches;
+        CU(launch_wavefront(c->tune, c->last_info, &c->wf, sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "wavefront launch");
     }
+    c->last_launches = c->last_info.launches;
     return RTB_OK;
 }
 
@@ -685,7 +688,7 @@ int rtb_frame_stats_get(rtb_context* c, rtb_frame_stats* out)
     Counters h;
     CU(cudaMemcpy(&h, c->counters_d, sizeof h, cudaMemcpyDeviceToHost), "counters");
     out->rays = h.rays; out->nodes_visited = h.nodes; out->tris_tested = h.tris; out->device_ms = c->last_ms; out->overflow = h.overflow;
-    out->launches = c->last_launches;
+    out->launches = c->last_launches; out->kernel_variant = c->last_info.variant;
     if (h.overflow) return fail(RTB_ERR_OVERFLOW, "render: traversal stack / ray queue overflow");
     return RTB_OK;
 }

@@ -13,8 +13,6 @@
 
 namespace rtb {
 
-float g_sah_node_cost = 1.0f;     // cost of one wide-node child box relative to one triangle test in the SAH leaf decision (option "sah_node", permille)
-
 // ------------------------------------------------------------------ arena
 cudaError_t Arena::reserve(size_t bytes)
 {
@@ -554,7 +552,7 @@ __global__ void k_emit_tris(const rtb_triangle* __restrict__ tris, int n, const 
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 
 template <typename K>
-static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
+static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, float sah_node_cost, BvhResult& out,
                               Arena& ws, BuildCounters* ctr, cudaStream_t st)
 {
     K* keys[2]; unsigned* vals[2];
@@ -576,17 +574,17 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     const unsigned* sorted = vals[cur];                                 // Morton order; out.order becomes the node-by-node order (k_collapse)
     k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
     CK(cudaMemsetAsync(visit, 0, sizeof(int) * (size_t)n, st));
-    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, sorted, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, g_sah_node_cost, 1.0f,
+    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, sorted, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, sah_node_cost, 1.0f,
                                                                    (int*)q0, ctr);
-    k_fit_top<<<148 * 4, 256, 0, st>>>((const int*)q0, ctr, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, g_sah_node_cost, 1.0f);
+    k_fit_top<<<148 * 4, 256, 0, st>>>((const int*)q0, ctr, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, sah_node_cost, 1.0f);
     k_root_sah<<<1, 1, 0, st>>>(nb_max, ctr);
     // level 0 work item: open binary root into wide node 0
     int2 root_item = make_int2(0, 0);
     CK(cudaMemcpyAsync(q0, &root_item, sizeof(int2), cudaMemcpyHostToDevice, st));
     int one = 1;
     CK(cudaMemcpyAsync(&ctr->qcount[0], &one, sizeof(int), cudaMemcpyHostToDevice, st));
-    static int resident = 0;                                            // CTAs of k_collapse that fit the device at once
-    if (!resident) {
+    int resident = 0;                                                   // CTAs of k_collapse that fit THIS device at once
+    {
         int dev = 0, sms = 0, per_sm = 0;
         CK(cudaGetDevice(&dev));
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -602,8 +600,8 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     return cudaGetLastError();
 }
 
-cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out, Arena& ws,
-                      cudaStream_t st, float4* tri_rec, float2* uvs, cudaEvent_t done)
+cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, float sah_node_cost, BvhResult& out,
+                      Arena& ws, cudaStream_t st, float4* tri_rec, float2* uvs, cudaEvent_t done)
 {
     // outputs (grow-only)
     int need_nodes = n > 1 ? n : 1;
@@ -636,9 +634,9 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
     if (n <= 1) {
         k_trivial_root<<<1, 1, 0, st>>>(out.nodes, bmin, bmax, n, out.order, ctr);
     } else if (wide_keys) {
-        CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 48, out, ws, ctr, st));
+        CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 48, sah_node_cost, out, ws, ctr, st));
     } else {
-        CK(build_tree<unsigned>(bmin, bmax, n, max_leaf, 32, out, ws, ctr, st));
+        CK(build_tree<unsigned>(bmin, bmax, n, max_leaf, 32, sah_node_cost, out, ws, ctr, st));
     }
     // triangle records in leaf order: enqueued BEFORE the counters are read back, so the device does not idle while the host
     // wakes up from the synchronisation below (one host round trip per build instead of two)

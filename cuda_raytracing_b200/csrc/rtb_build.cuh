@@ -29,14 +29,13 @@ struct BvhResult {
     float sah = 0.f;
 };
 
-extern float g_sah_node_cost;
-
 // Builds a wide BVH over n primitive boxes (device float4 arrays, w ignored).  With `tris_dev` the boxes are first made from
 // those n triangles (written to bmin/bmax, fused with the scene-bounds reduction); without, bmin/bmax are the input.
 // With `tri_rec`/`uvs` as well, the 64-byte triangle records and the uvs are written in leaf order (k_emit_tris).
 // `done` (optional) is recorded after the last kernel.  Asynchronous on `st` except for one small read-back of the build
 // counters at the end.
-cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, BvhResult& out,
+// sah_node_cost: cost of one wide-node child box relative to one triangle test in the SAH leaf decision (option "sah_node").
+cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, float sah_node_cost, BvhResult& out,
                       Arena& ws, cudaStream_t st, float4* tri_rec = nullptr, float2* uvs = nullptr, cudaEvent_t done = nullptr);
 
 

@@ -29,6 +29,7 @@ struct MegaBufs {
     float4* sp1 = nullptr;          //                       (base colour, cos)
     float4* cont_o = nullptr;       // continuation ray origin, .w = 1 when the chain continues after the shadow ray
     float4* cont_d = nullptr;       // continuation ray direction
+    unsigned* pix = nullptr;        // finished pixels, b | g << 8 | r << 16, indexed y * width + x (k_emit_frame writes the frame)
 };
 
 struct MegaState {
@@ -39,7 +40,7 @@ struct MegaState {
     float4* q_org = nullptr; float4* q_dir = nullptr;   // ray ring of the queue variant (k_megaq)
     unsigned* q_ticket = nullptr; unsigned* q_ctl = nullptr;
     size_t q_cap = 0;
-    size_t cap = 0;
+    size_t cap = 0, pix_cap = 0;
     int nb_cap = 0;
     // the cost map is only reused when the next frame has the same pixel set
     int hist_w = 0, hist_h = 0, hist_rank = -1, hist_count = 0, hist_mode = -1;
@@ -274,10 +275,8 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
             }
             if (ended) {                                        // radiance -> 8-bit BGR pixel (PATH: mean over samples)
                 const float scale = PATH ? 1.0f / (float)P.spp : 1.0f;
-                unsigned char* p = img + (size_t)y * pitch + 3 * (size_t)x;
-                p[0] = to_u8(xm(clamp01(xm(acc.x, scale)), 255.0f));
-                p[1] = to_u8(xm(clamp01(xm(acc.y, scale)), 255.0f));
-                p[2] = to_u8(xm(clamp01(xm(acc.z, scale)), 255.0f));
+                B.pix[(size_t)y * P.width + x] = (unsigned)to_u8(xm(clamp01(xm(acc.x, scale)), 255.0f)) | ((unsigned)to_u8(xm(clamp01(xm(acc.y, scale)), 255.0f)) << 8) |
+                                                 ((unsigned)to_u8(xm(clamp01(xm(acc.z, scale)), 255.0f)) << 16);
                 if ((idx & 7) == 0) atomicAdd(G.cost + blk, steps);       // 1 pixel in 8 reports: the map is a heuristic, the atomics are not free
                 idx = -1;
             }
@@ -332,7 +331,12 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
 //     few, so the head/tail words are shared by ~10 CTAs instead of all 1184 (one global ring livelocks on its CAS).
 //   * producers reserve slots with atomicAdd(tail), write the 32-byte entry, fence, publish ticket[slot] = position+1;
 //     consumers reserve with atomicCAS(head) only below the tail they read, spin on the ticket, fence, read with ld.cg.
+//     Positions run on from frame to frame (a frame ends with head == tail in every ring), so a ticket can never be
+//     mistaken for one of an earlier frame and the ticket array is cleared once, when it is allocated -- not per frame.
 //   * a full ring never blocks: the producing lanes keep their rays and trace them themselves (k_mega's behaviour).
+//     "Full" leaves QR_MARGIN entries free: a consumer holds a claim of <= 32 entries between its CAS and its loads, a ring
+//     is consumed by the CTAs of 4 consecutive ring numbers (<= 4 * ceil(grid / QR_RINGS) CTAs * 4 warps = 160 warps at
+//     the largest grid = 5120 entries), and a producer must not lap an entry that is claimed but not yet read.
 //   * once every tile is claimed nothing is enqueued any more (the frame tail is latency-bound: a queue hop only delays
 //     the chain); a warp leaves when no tile is unclaimed and every ring is empty.  A ray enqueued concurrently with that
 //     check is never stranded: its producer passes through the fetch path right after the enqueue and finds it.
@@ -341,6 +345,7 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
 #endif
 constexpr int QR_RINGS = RTB_QR_RINGS;
 constexpr int QR_CTL = 64;                      // unsigned words per ring control block: [0] head, [32] tail (separate lines)
+constexpr unsigned QR_MARGIN = 8192;            // entries a producer leaves free (see above); rings hold >= 2 * QR_MARGIN entries
 struct QRing {
     float4* org;                    // [QR_RINGS][cap] (origin, pixel slot)
     float4* dir;                    // [QR_RINGS][cap] (direction, meta)
@@ -397,10 +402,8 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
             if (next) st_stream(B.acc + idx, make_float4(R.acc.x, R.acc.y, R.acc.z, 0.f));
             if (ended) {                                        // radiance -> 8-bit BGR pixel (PATH: mean over samples)
                 const float scale = PATH ? 1.0f / (float)P.spp : 1.0f;
-                unsigned char* p = img + (size_t)R.y * pitch + 3 * (size_t)R.x;
-                p[0] = to_u8(xm(clamp01(xm(R.acc.x, scale)), 255.0f));
-                p[1] = to_u8(xm(clamp01(xm(R.acc.y, scale)), 255.0f));
-                p[2] = to_u8(xm(clamp01(xm(R.acc.z, scale)), 255.0f));
+                B.pix[(size_t)R.y * P.width + R.x] = (unsigned)to_u8(xm(clamp01(xm(R.acc.x, scale)), 255.0f)) | ((unsigned)to_u8(xm(clamp01(xm(R.acc.y, scale)), 255.0f)) << 8) |
+                                                     ((unsigned)to_u8(xm(clamp01(xm(R.acc.z, scale)), 255.0f)) << 16);
             }
         }
         const unsigned nm = __ballot_sync(0xffffffffu, next);
@@ -413,7 +416,7 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
             if (lane == leader && __popc(nm) < keep_thr && *(volatile int*)head < G.n_slots) {
                 unsigned* c = Q.ctl + (size_t)r0 * QR_CTL;
                 const unsigned used = ld_volatile_u32(c + 32) - ld_volatile_u32(c);
-                if (used + 4096u <= Q.cap) base = atomicAdd(c + 32, (unsigned)__popc(nm));   // margin > every sharing warp's 32
+                if (used + QR_MARGIN <= Q.cap) base = atomicAdd(c + 32, (unsigned)__popc(nm));
             }
             base = __shfl_sync(0xffffffffu, base, leader);
             kept = base == 0xffffffffu;
@@ -460,7 +463,9 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
                     const unsigned hm = __ballot_sync(0xffffffffu, has);
                     const int any_r = hm ? __shfl_sync(0xffffffffu, mine, __ffs(hm) - 1) : -1;
                     if (lane == 0) {
-                        if (any_r < 0 || tries > (1 << 16)) got = 3;
+                        const bool stuck = any_r >= 0 && tries > (1 << 16);
+                        if (stuck) ctr->overflow = 1;           // rays left behind: the frame is reported as failed
+                        if (any_r < 0 || stuck) got = 3;
                         else { qn = ring_try_claim(Q, any_r, true, qbase); if (qn) { got = 1; qr = any_r; } }
                     }
                 }
@@ -473,13 +478,16 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
                     const unsigned pos = qbase + (unsigned)lane, slot = pos & (Q.cap - 1u);
                     const size_t e = (size_t)qr * Q.cap + slot;
                     unsigned wait = 0;
-                    while (ld_volatile_u32(Q.ticket + e) != pos + 1u) { if (++wait > (1u << 26)) { ctr->overflow = 1; break; } }
-                    __threadfence();
-                    const float4 o = ld_stream(Q.org + e), d = ld_stream(Q.dir + e);
-                    idx = __float_as_int(o.w); meta = __float_as_uint(d.w);
-                    sink.reset(idx, (meta & 1u) != 0u);
-                    S.begin(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), stk);
-                    rays++;
+                    bool published = true;
+                    while (ld_volatile_u32(Q.ticket + e) != pos + 1u) { if (++wait > (1u << 26)) { ctr->overflow = 1; published = false; break; } }
+                    if (published) {                            // an entry that never appears is dropped (frame reported as failed), not read
+                        __threadfence();
+                        const float4 o = ld_stream(Q.org + e), d = ld_stream(Q.dir + e);
+                        idx = __float_as_int(o.w); meta = __float_as_uint(d.w);
+                        sink.reset(idx, (meta & 1u) != 0u);
+                        S.begin(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), stk);
+                        rays++;
+                    }
                 }
             } else {
                 pbase = __shfl_sync(0xffffffffu, pbase, 0);
@@ -502,12 +510,22 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
     if (lane == 0 && rays) atomicAdd(&ctr->rays, (unsigned long long)rays);
 }
 
+// Start of a frame: the pixel-slot counter back to 0; ring positions run on (no ticket reset).  A frame that ended normally
+// left head == tail in every ring; one that was cut short (overflow flag) may not have: whatever it left is dropped here.
+__global__ void k_frame_begin(int* __restrict__ head, unsigned* __restrict__ ctl, int rings)
+{
+    if (threadIdx.x == 0) *head = 0;
+    if (ctl && (int)threadIdx.x < rings) { unsigned* c = ctl + (size_t)threadIdx.x * QR_CTL; c[0] = c[32]; }
+}
+
 #define MCK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 
 static void mega_free(MegaState* m)
 {
     float4** bufs[] = { &m->b.acc, &m->b.thr, &m->b.hit0, &m->b.hit1, &m->b.sp0, &m->b.sp1, &m->b.cont_o, &m->b.cont_d };
     for (auto p : bufs) { if (*p) cudaFree(*p); *p = nullptr; }
+    if (m->b.pix) cudaFree(m->b.pix);
+    m->b.pix = nullptr; m->pix_cap = 0;
     if (m->head) cudaFree(m->head);
     if (m->cost) cudaFree(m->cost);
     if (m->order) cudaFree(m->order);
@@ -527,10 +545,7 @@ void mega_release(void* state)
     delete m;
 }
 
-extern int g_wave_launches;
-static int g_wave_launches_pre = 0;
-
-cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
+cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
                         const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st)
 {
     MegaState* m = (MegaState*)*state;
@@ -555,34 +570,39 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
         MCK(cudaMalloc((void**)&m->order, sizeof(int) * (size_t)G.nb));
         m->cap = (size_t)G.n_slots; m->nb_cap = G.nb;
     }
+    if (m->pix_cap < (size_t)P.width * P.height) {
+        if (m->b.pix) cudaFree(m->b.pix);
+        m->b.pix = nullptr; m->pix_cap = 0;
+        MCK(cudaMalloc((void**)&m->b.pix, sizeof(unsigned) * (size_t)P.width * P.height));
+        m->pix_cap = (size_t)P.width * P.height;
+    }
     // The queue variant wins when the frame is long enough to amortise its tail (measured on C3: 4.1 M slots 4.92 vs 5.12 ms,
     // 2.1 M slots 3.10 vs 2.86 ms) and always for path tracing, whose chains run for spp samples (C4 at 1/8: 9.3 vs 10.3 ms).
-    const int variant = g_tune.fused >= 0 ? g_tune.fused : (path || G.n_slots >= 3000000 ? 2 : 1);
-    const bool have_hist = variant == 1 && g_tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
+    const int variant = tune.fused >= 0 ? tune.fused : (path || G.n_slots >= 3000000 ? 2 : 1);
+    const bool have_hist = variant == 1 && tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
                            m->hist_count == P.tile_count && m->hist_mode == P.mode;
-    if (have_hist) { k_order<<<1, 1024, 0, st>>>(m->cost, G.nb, m->order); g_wave_launches_pre = 1; }
-    else { MCK(cudaMemsetAsync(m->cost, 0, sizeof(unsigned) * (size_t)G.nb, st)); g_wave_launches_pre = 0; }
+    info.launches = 0; info.variant = variant;
+    if (have_hist) { k_order<<<1, 1024, 0, st>>>(m->cost, G.nb, m->order); info.launches = 1; }
+    else MCK(cudaMemsetAsync(m->cost, 0, sizeof(unsigned) * (size_t)G.nb, st));
     G.order = have_hist ? m->order : nullptr;
     G.cost = m->cost;
     m->hist_w = variant == 1 ? P.width : 0;                              // the queue variant keeps no cost map
     m->hist_h = P.height; m->hist_rank = P.tile_rank; m->hist_count = P.tile_count; m->hist_mode = P.mode;
-    MCK(cudaMemsetAsync(m->head, 0, sizeof(int), st));
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    g_wave_launches = g_wave_launches_pre;
     if (path && (aov.prim || aov.inst || aov.t)) {
         FrameParams Q = P; Q.mode = RTB_MODE_REFERENCE;                 // first-hit AOVs from the un-jittered centre ray
-        MCK(launch_render(sc, Q, img, pitch, aov, ctr, count, st));
-        g_wave_launches++;
+        MCK(launch_render(tune, sc, Q, img, pitch, aov, ctr, count, st));
+        info.launches++;
     }
-    const int mb = g_tune.trace_minb <= 4 ? 4 : (g_tune.trace_minb == 5 ? 5 : (g_tune.trace_minb == 6 ? 6 : 8));
-    const int ri = g_tune.refill_idle;
+    const int mb = tune.trace_minb <= 4 ? 4 : (tune.trace_minb == 5 ? 5 : (tune.trace_minb == 6 ? 6 : 8));
+    const int ri = tune.refill_idle;
     const int grid = std::min(sms * (count ? 4 : mb), (G.n_slots + 127) / 128);
     const bool smem = sc.top_tlas_n + sc.top_blas_n > 0;
     const size_t shb = smem ? (size_t)(sc.top_tlas_n + sc.top_blas_n) * NODE_F4 * 16 + 16 : 0;
     if (variant == 2) {                                                 // in-kernel ray queue variant
-        size_t qcap = 8192;                                             // entries per ring; a full ring falls back to in-lane tracing
+        size_t qcap = 2 * QR_MARGIN;                                    // entries per ring; a full ring falls back to in-lane tracing
         while (qcap * QR_RINGS < 2 * (size_t)G.n_slots) qcap <<= 1;
         if (m->q_cap < qcap) {
             if (m->q_org) cudaFree(m->q_org);
@@ -595,30 +615,36 @@ cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, 
             MCK(cudaMalloc((void**)&m->q_ticket, sizeof(unsigned) * qcap * QR_RINGS));
             MCK(cudaMalloc((void**)&m->q_ctl, sizeof(unsigned) * (QR_RINGS * QR_CTL + 32)));
             m->q_cap = qcap;
+            MCK(cudaMemsetAsync(m->q_ticket, 0, sizeof(unsigned) * m->q_cap * QR_RINGS, st));      // once per allocation
+            MCK(cudaMemsetAsync(m->q_ctl, 0, sizeof(unsigned) * (QR_RINGS * QR_CTL + 32), st));
         }
-        MCK(cudaMemsetAsync(m->q_ticket, 0, sizeof(unsigned) * m->q_cap * QR_RINGS, st));
-        MCK(cudaMemsetAsync(m->q_ctl, 0, sizeof(unsigned) * (QR_RINGS * QR_CTL + 32), st));
+        k_frame_begin<<<1, 128, 0, st>>>(m->head, m->q_ctl, QR_RINGS);
+        info.launches++;
         QRing Q;
         Q.org = m->q_org; Q.dir = m->q_dir; Q.ticket = m->q_ticket; Q.ctl = m->q_ctl;
         Q.cap = (unsigned)m->q_cap;
         MegaGeo GQ = G;
         GQ.order = nullptr;                                             // no cost map in this variant
-#define RTB_MEGAQ(PATH, COUNT, MINB) k_megaq<PATH, COUNT, MINB><<<grid, 128, 0, st>>>(g_tune.queue_keep, sc, P, GQ, m->head, Q, m->b, img, pitch, aov.prim, aov.inst, aov.t, ctr)
+#define RTB_MEGAQ(PATH, COUNT, MINB) k_megaq<PATH, COUNT, MINB><<<grid, 128, 0, st>>>(tune.queue_keep, sc, P, GQ, m->head, Q, m->b, img, pitch, aov.prim, aov.inst, aov.t, ctr)
 #define RTB_MEGAQ_MB(PATH) do { if (count) RTB_MEGAQ(PATH, true, 4); else if (mb <= 5) RTB_MEGAQ(PATH, false, 5); \
                                 else if (mb == 6) RTB_MEGAQ(PATH, false, 6); else RTB_MEGAQ(PATH, false, 8); } while (0)
         if (path) RTB_MEGAQ_MB(true); else RTB_MEGAQ_MB(false);
-        g_wave_launches++;
-        return cudaGetLastError();
+        info.launches += 2;
+        MCK(cudaGetLastError());
+        return launch_emit_frame<true>(P, 1.0f, m->b.pix, nullptr, img, pitch, st);
     }
-#define RTB_MEGA(PATH, COUNT, MINB) do { if (smem) k_mega<PATH, COUNT, MINB, true><<<grid, 128, shb, st>>>(ri, g_tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
+    k_frame_begin<<<1, 128, 0, st>>>(m->head, nullptr, 0);
+    info.launches++;
+#define RTB_MEGA(PATH, COUNT, MINB) do { if (smem) k_mega<PATH, COUNT, MINB, true><<<grid, 128, shb, st>>>(ri, tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
                                                                                      aov.prim, aov.inst, aov.t, ctr); \
-                                         else k_mega<PATH, COUNT, MINB, false><<<grid, 128, 0, st>>>(ri, g_tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
+                                         else k_mega<PATH, COUNT, MINB, false><<<grid, 128, 0, st>>>(ri, tune.tail_idle, sc, P, G, m->head, m->b, img, pitch, \
                                                                                      aov.prim, aov.inst, aov.t, ctr); } while (0)
 #define RTB_MEGA_MB(PATH) do { if (count) RTB_MEGA(PATH, true, 4); else if (mb == 4) RTB_MEGA(PATH, false, 4); else if (mb == 5) RTB_MEGA(PATH, false, 5); \
                                else if (mb == 6) RTB_MEGA(PATH, false, 6); else RTB_MEGA(PATH, false, 8); } while (0)
     if (path) RTB_MEGA_MB(true); else RTB_MEGA_MB(false);
-    g_wave_launches++;
-    return cudaGetLastError();
+    info.launches += 2;
+    MCK(cudaGetLastError());
+    return launch_emit_frame<true>(P, 1.0f, m->b.pix, nullptr, img, pitch, st);
 }
 
 }  // namespace rtb

@@ -8,8 +8,6 @@
 
 namespace rtb {
 
-Tune g_tune;
-
 XF void write_pixel(unsigned char* img, size_t pitch, int x, int y, unsigned char b, unsigned char g, unsigned char r)
 {
     unsigned char* p = img + (size_t)y * pitch + 3 * (size_t)x;
@@ -79,7 +77,7 @@ __global__ void __launch_bounds__(128, MINB) k_render_direct(SceneDev sc, FrameP
     if (lane == 0 && rays) atomicAdd(&ctr->rays, (unsigned long long)rays);
 }
 
-cudaError_t launch_render(const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch, const rtb_aovs& aov,
+cudaError_t launch_render(const Tune& tune, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch, const rtb_aovs& aov,
                           Counters* ctr, bool count, cudaStream_t st)
 {
     const int bands = (P.height + BAND_ROWS - 1) / BAND_ROWS;
@@ -91,7 +89,7 @@ cudaError_t launch_render(const SceneDev& sc, const FrameParams& P, unsigned cha
 #define RTB_DIRECT(LIT, COUNT, MINB) k_render_direct<LIT, COUNT, MINB><<<grid, 128, 0, st>>>(sc, P, img, pitch, aov.prim, aov.inst, aov.t, ctr)
     if (count) { if (lit) RTB_DIRECT(true, true, 4); else RTB_DIRECT(false, true, 4); }
     else {
-        const int mb = g_tune.direct_minb;
+        const int mb = tune.direct_minb;
         if (lit) { if (mb <= 4) RTB_DIRECT(true, false, 4); else if (mb == 5) RTB_DIRECT(true, false, 5); else if (mb == 6) RTB_DIRECT(true, false, 6); else RTB_DIRECT(true, false, 8); }
         else { if (mb <= 4) RTB_DIRECT(false, false, 4); else if (mb == 5) RTB_DIRECT(false, false, 5); else if (mb == 6) RTB_DIRECT(false, false, 6); else RTB_DIRECT(false, false, 8); }
     }

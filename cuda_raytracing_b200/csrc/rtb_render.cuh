@@ -4,7 +4,7 @@
 
 namespace rtb {
 
-// Tuning knobs (rtb_set_option "trace_minb" / "direct_minb" / "refill_idle"); process-wide, read at launch time.
+// Tuning knobs (rtb_set_option "trace_minb" / "direct_minb" / "refill_idle" ...); one set per context, read at launch time.
 struct Tune {
     int trace_minb = 8;     // __launch_bounds__(128, N) variant of the queue tracer: resident blocks per SM the registers allow
     int direct_minb = 8;    // same for the direct kernel
@@ -17,9 +17,13 @@ struct Tune {
     int spec_thr = 4;       // see SceneDev::spec_thr
     int refill_idle = 32;   // queue tracer: refill a warp once this many lanes are idle
 };
-extern Tune g_tune;
+// what a frame launched: filled by the launchers, reported through rtb_frame_stats
+struct LaunchInfo {
+    int launches = 0;       // kernels of this library launched for the frame
+    int variant = -1;       // modes 2/3: 2 = k_megaq, 1 = k_mega, 0 = staged wavefront; -1 = the direct kernel
+};
 
-cudaError_t launch_render(const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch, const rtb_aovs& aov,
+cudaError_t launch_render(const Tune& tune, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch, const rtb_aovs& aov,
                           Counters* ctr, bool count, cudaStream_t st);
 
 }  // namespace rtb

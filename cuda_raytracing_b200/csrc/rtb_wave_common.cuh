@@ -52,4 +52,68 @@ XF bool local_to_pixel(const FrameParams& P, int idx, int tiles_x, int& x, int& 
     return x < P.width && y < P.height;
 }
 
+// ------------------------------------------------------------------ frame emission with 16-byte stores
+// The persistent kernels finish pixels one at a time, in any order, so they do not write the frame: a finished pixel goes to a
+// rank-local staging array as ONE packed word (b | g << 8 | r << 16; the staged pipeline leaves its radiance sums instead) and
+// this pass, one thread per 16 pixels of a row, turns them into three aligned 16-byte stores (48 bytes = 16 BGR pixels).  At
+// N > 1 the frame may be rank 0's memory mapped over NVLink: the link then carries 16-byte stores, not single bytes (the
+// reference stores three bytes per pixel, raycast.cu:292-294).
+template <bool PACKED>
+__global__ void __launch_bounds__(256) k_emit_frame(FrameParams P, int my_rows, int chunks, float scale, const unsigned* __restrict__ pix,
+                                                    const float4* __restrict__ acc, unsigned char* __restrict__ img, size_t pitch)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= my_rows * chunks) return;
+    const int r = t / chunks, c = t - r * chunks;
+    const int y = ((r / BAND_ROWS) * P.tile_count + P.tile_rank) * BAND_ROWS + (r % BAND_ROWS);
+    if (y >= P.height) return;
+    const int x0 = 16 * c, n = min(16, P.width - x0);
+    const size_t row = (size_t)y * P.width + x0;
+    unsigned px[16];
+    if (PACKED && n == 16 && (P.width & 3) == 0) {
+        const uint4* q = (const uint4*)(pix + row);
+#pragma unroll
+        for (int i = 0; i < 4; i++) { const uint4 v = __ldcg(q + i); px[4 * i] = v.x; px[4 * i + 1] = v.y; px[4 * i + 2] = v.z; px[4 * i + 3] = v.w; }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            px[i] = 0u;
+            if (i < n) {
+                if (PACKED) px[i] = __ldcg(pix + row + i);
+                else {
+                    const float4 a = __ldcg(acc + row + i);
+                    px[i] = (unsigned)to_u8(xm(clamp01(xm(a.x, scale)), 255.0f)) | ((unsigned)to_u8(xm(clamp01(xm(a.y, scale)), 255.0f)) << 8) |
+                            ((unsigned)to_u8(xm(clamp01(xm(a.z, scale)), 255.0f)) << 16);
+                }
+            }
+        }
+    }
+    unsigned char* dst = img + (size_t)y * pitch + 3 * (size_t)x0;
+    if (n == 16 && (((size_t)img | pitch) & 15) == 0) {
+        unsigned w[12];
+#pragma unroll
+        for (int g = 0; g < 4; g++) {                       // 4 pixels -> 3 words
+            const unsigned p0 = px[4 * g], p1 = px[4 * g + 1], p2 = px[4 * g + 2], p3 = px[4 * g + 3];
+            w[3 * g] = (p0 & 0xffffffu) | (p1 << 24);
+            w[3 * g + 1] = ((p1 >> 8) & 0xffffu) | (p2 << 16);
+            w[3 * g + 2] = ((p2 >> 16) & 0xffu) | (p3 << 8);
+        }
+        uint4* d4 = (uint4*)dst;
+        d4[0] = make_uint4(w[0], w[1], w[2], w[3]); d4[1] = make_uint4(w[4], w[5], w[6], w[7]); d4[2] = make_uint4(w[8], w[9], w[10], w[11]);
+    } else {
+        for (int i = 0; i < n; i++) { dst[3 * i] = (unsigned char)px[i]; dst[3 * i + 1] = (unsigned char)(px[i] >> 8); dst[3 * i + 2] = (unsigned char)(px[i] >> 16); }
+    }
+}
+
+template <bool PACKED>
+inline cudaError_t launch_emit_frame(const FrameParams& P, float scale, const unsigned* pix, const float4* acc, unsigned char* img, size_t pitch, cudaStream_t st)
+{
+    const int bands = (P.height + BAND_ROWS - 1) / BAND_ROWS;
+    const int my_bands = (bands - P.tile_rank + P.tile_count - 1) / P.tile_count;
+    if (my_bands <= 0) return cudaSuccess;
+    const int my_rows = my_bands * BAND_ROWS, chunks = (P.width + 15) / 16;
+    k_emit_frame<PACKED><<<(my_rows * chunks + 255) / 256, 256, 0, st>>>(P, my_rows, chunks, scale, pix, acc, img, pitch);
+    return cudaGetLastError();
+}
+
 }  // namespace rtb

@@ -10,7 +10,7 @@
 //   k_shade        hit record -> material, radiance bookkeeping; appends the shadow ray and the continuation ray to
 //                  their queues with warp-ballot compaction
 //   k_trace_queue<ANY>  shadow rays (any-hit), adds the lit / shadowed Lambert term to the pixel
-// and k_resolve converts the per-pixel radiance to the 8-bit BGR frame.
+// and k_emit_frame (rtb_wave_common.cuh) converts the per-pixel radiance to the 8-bit BGR frame.
 // Queue records: ray 2 x float4 (origin|pixel, direction), hit 2 x float4 (min,u,v,inst | location,slot),
 // shadow 3 x float4 (origin|pixel, throughput|w, colour|cos).  Per-pixel throughput / radiance: float4 arrays.
 #include "rtb_wave_common.cuh"
@@ -34,7 +34,7 @@ struct WaveState {
     void* mega = nullptr;           // state of the fused persistent kernel (rtb_mega.cu)
 };
 
-cudaError_t launch_mega(void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
+cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
                         const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st);
 void mega_release(void* state);
 
@@ -267,19 +267,6 @@ __global__ void __launch_bounds__(128) k_shade(SceneDev sc, FrameParams P, int b
     }
 }
 
-// radiance -> 8-bit BGR pixel (REFLECT: sum of the chain; PATH: mean over samples)
-__global__ void k_resolve(FrameParams P, int n_local, int tiles_x, float scale, const float4* __restrict__ acc,
-                          unsigned char* __restrict__ img, size_t pitch)
-{
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= n_local) return;
-    int x, y;
-    if (!local_to_pixel(P, idx, tiles_x, x, y)) return;
-    const float4 a = acc[y * P.width + x];
-    unsigned char* p = img + (size_t)y * pitch + 3 * (size_t)x;
-    p[0] = to_u8(xm(clamp01(xm(a.x, scale)), 255.0f)); p[1] = to_u8(xm(clamp01(xm(a.y, scale)), 255.0f)); p[2] = to_u8(xm(clamp01(xm(a.z, scale)), 255.0f));
-}
-
 #define WCK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 
 static void wave_free(WaveState* w)
@@ -290,14 +277,12 @@ static void wave_free(WaveState* w)
     w->counters = nullptr; w->cap_rays = w->cap_pixels = 0; w->n_counters = 0;
 }
 
-int g_wave_launches = 0;
-
-cudaError_t launch_wavefront(rtb_context*, void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
+cudaError_t launch_wavefront(const Tune& tune, LaunchInfo& info, void** state, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
                              const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st)
 {
     WaveState* w = (WaveState*)*state;
     if (!w) { w = new WaveState(); *state = w; }
-    if (g_tune.fused) return launch_mega(&w->mega, sc, P, img, pitch, aov, ctr, count, st);
+    if (tune.fused) return launch_mega(tune, info, &w->mega, sc, P, img, pitch, aov, ctr, count, st);
     const bool path = P.mode == RTB_MODE_PATH;
     const int bands = (P.height + BAND_ROWS - 1) / BAND_ROWS;
     const int my_bands = (bands - P.tile_rank + P.tile_count - 1) / P.tile_count;
@@ -321,22 +306,22 @@ cudaError_t launch_wavefront(rtb_context*, void** state, const SceneDev& sc, con
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int mb = g_tune.trace_minb <= 4 ? 4 : (g_tune.trace_minb == 5 ? 5 : (g_tune.trace_minb == 6 ? 6 : 8));
-    const int ri = g_tune.refill_idle;
+    const int mb = tune.trace_minb <= 4 ? 4 : (tune.trace_minb == 5 ? 5 : (tune.trace_minb == 6 ? 6 : 8));
+    const int ri = tune.refill_idle;
     const int grid_t = sms * (count ? 4 : mb), grid_s = grid_t;
     const int grid_shade = std::min(sms * 8, (n_local + 127) / 128);
     const float3 L = P.light_dir;
-    g_wave_launches = 0;
+    info.launches = 0; info.variant = 0;
     if (path && (aov.prim || aov.inst || aov.t)) {
         FrameParams Q = P; Q.mode = RTB_MODE_REFERENCE;                 // first-hit AOVs from the un-jittered centre ray
-        WCK(launch_render(sc, Q, img, pitch, aov, ctr, count, st));
-        g_wave_launches++;
+        WCK(launch_render(tune, sc, Q, img, pitch, aov, ctr, count, st));
+        info.launches++;
     }
     for (int s = 0; s < passes; s++) {
         int* c0 = w->counters + 4 * s * per_pass;
         if (path) k_gen<true><<<(n_local + 255) / 256, 256, 0, st>>>(P, s, n_local, tiles_x, w->q_org[0], w->q_dir[0], c0);
         else k_gen<false><<<(n_local + 255) / 256, 256, 0, st>>>(P, s, n_local, tiles_x, w->q_org[0], w->q_dir[0], c0);
-        g_wave_launches++;
+        info.launches++;
         for (int b = 0; b <= P.max_depth; b++) {
             int* c4 = c0 + 4 * b;
 #define RTB_TQ(ANY, COUNT, MINB, GRID, ...) k_trace_queue<ANY, COUNT, MINB><<<GRID, 128, 0, st>>>(ri, sc, __VA_ARGS__)
@@ -346,16 +331,16 @@ cudaError_t launch_wavefront(rtb_context*, void** state, const SceneDev& sc, con
             RTB_TQ_MB(false, grid_t, w->q_org[b & 1], w->q_dir[b & 1], L, c4 + 0, c4 + 1, w->hit0, w->hit1, nullptr, nullptr, nullptr, ctr);
             if (path) k_shade<true><<<grid_shade, 128, 0, st>>>(sc, P, b, s, *w, c4, aov.prim, aov.inst, aov.t);
             else k_shade<false><<<grid_shade, 128, 0, st>>>(sc, P, b, s, *w, c4, aov.prim, aov.inst, aov.t);
-            g_wave_launches += 2;
+            info.launches += 2;
             if (!path) {
                 RTB_TQ_MB(true, grid_s, w->s_org, nullptr, L, c4 + 2, c4 + 3, nullptr, nullptr, w->s_p0, w->s_p1, w->acc, ctr);
-                g_wave_launches++;
+                info.launches++;
             }
         }
     }
-    k_resolve<<<(n_local + 255) / 256, 256, 0, st>>>(P, n_local, tiles_x, path ? 1.0f / (float)P.spp : 1.0f, w->acc, img, pitch);
-    g_wave_launches++;
-    return cudaGetLastError();
+    // radiance -> 8-bit BGR frame (REFLECT: sum of the chain; PATH: mean over samples), 16-byte stores
+    info.launches++;
+    return launch_emit_frame<false>(P, path ? 1.0f / (float)P.spp : 1.0f, nullptr, w->acc, img, pitch, st);
 }
 
 void wave_release(void* state)

@@ -90,6 +90,8 @@ typedef struct {
     float device_ms;           /* cudaEvent time of the last rtb_render_host / rtb_render_timed             */
     int overflow;              /* traversal stack or queue overflow flag (render fails loudly)              */
     int launches;              /* kernels of this library launched by the last rtb_render                   */
+    int kernel_variant;        /* modes 2/3: 2 = persistent kernel with in-kernel ray queues, 1 = persistent kernel,
+                                  0 = staged wavefront pipeline; -1 = the direct kernel (modes 0/1)           */
 } rtb_frame_stats;
 
 /* ---- context ------------------------------------------------------------------------------ */

@@ -526,10 +526,14 @@ typedef struct { uint64_t nodes, boxes, tris; } ctr_t;
 
 /* raycast.cu:21-142 cast_ray.  `any_hit` is the commented-out lighting_pass early return
  * (raycast.cu:128-132): the shadow query only asks whether min stayed FLT_MAX. */
+static void cast_ray_exhaustive_hit(const o_scene* sc, o_f3 origin, o_f3 direction, hit_t* hit, int any_hit);
+static int g_exhaustive = 0;     /* test support, see o_set_exhaustive below */
+
 static void cast_ray(const o_scene* sc, o_f3 origin, o_f3 direction, hit_t* hit, int any_hit, ctr_t* ctr)
 {
     hit->min = FLT_MAX; hit->prim = -1; hit->inst = -1; hit->material = -1;
     hit->location = f3(0, 0, 0); hit->normal = f3(0, 0, 0); hit->uv.x = hit->uv.y = 0;
+    if (g_exhaustive) { cast_ray_exhaustive_hit(sc, origin, direction, hit, any_hit); return; }
     for (int mesh_idx = 0; mesh_idx < sc->num_instances; mesh_idx++) {
         const o_instance* mi = &sc->instances[mesh_idx];
         const o_mesh* mesh = sc->meshes[mi->mesh_index];
@@ -602,6 +606,93 @@ int o_cast_ray(const o_scene* sc, o_f3 origin, o_f3 direction, int* prim, int* i
     return h.min != FLT_MAX;
 }
 
+/* ---- test support for the parity report (no counterpart in the reference): why does a pixel differ? ----
+ * o_candidate: the accept predicate of raycast.cu:87-109 for ONE (instance, triangle) pair -- 1 and the world distance when the
+ * candidate passes ray_intersect + point_inside + the front-face rule, else 0.
+ * o_cast_ray_exhaustive: the closest candidate over ALL instances and triangles with no BVH at all, i.e. what cast_ray returns
+ * when no box test ever culls; ties go to the lowest (instance, triangle), the product's documented tie-break. */
+static int candidate(const o_instance* mi, const o_mesh* mesh, const ray_t* r_ray, o_f3 origin, int index, float* distance)
+{
+    const o_tri* tri = &mesh->triangles[index];
+    o_f3 isect;
+    o_f2 uv;
+    if (!tri_ray_intersect(tri, r_ray, &isect)) return 0;
+    if (isect.x == FLT_MAX) return 0;
+    if (!tri_point_inside(tri, isect, &uv)) return 0;
+    o_f3 loc = f3(isect.x * mi->scale.x, isect.y * mi->scale.y, isect.z * mi->scale.z);
+    loc = o_apply_lre(mi->inv_pose, loc);
+    *distance = magnitude3(sub3(loc, origin));
+    return dot3(r_ray->direction, tri->normal) < 0;
+}
+
+static ray_t instance_ray(const o_instance* mi, o_f3 origin, o_f3 direction)
+{
+    o_f3 r_direction = o_apply_euler(mi->rotation, direction);
+    r_direction.x *= mi->inv_scale.x; r_direction.y *= mi->inv_scale.y; r_direction.z *= mi->inv_scale.z;
+    o_f3 r_origin = o_apply_lre(mi->pose, origin);
+    r_origin.x *= mi->inv_scale.x; r_origin.y *= mi->inv_scale.y; r_origin.z *= mi->inv_scale.z;
+    return make_ray(r_origin, r_direction);
+}
+
+int o_candidate(const o_scene* sc, o_f3 origin, o_f3 direction, int inst, int prim, float* distance)
+{
+    if (inst < 0 || inst >= sc->num_instances) return 0;
+    const o_instance* mi = &sc->instances[inst];
+    const o_mesh* mesh = sc->meshes[mi->mesh_index];
+    if (prim < 0 || prim >= mesh->num_triangles) return 0;
+    ray_t r = instance_ray(mi, origin, direction);
+    return candidate(mi, mesh, &r, origin, prim, distance);
+}
+
+/* o_set_exhaustive(1): every cast_ray of o_render / o_render_pixel becomes the BVH-free search below (all triangles of all
+ * instances, ties to the lowest (instance, triangle)): "what the reference's accept rule yields when no box test culls".  The
+ * parity suite uses it to show that a pixel on which product and reference differ is one where the reference's own culling
+ *  or its traversal-order tie-break (H5) decided -- never to produce expected values. */
+void o_set_exhaustive(int on) { g_exhaustive = on; }
+
+static void cast_ray_exhaustive_hit(const o_scene* sc, o_f3 origin, o_f3 direction, hit_t* hit, int any_hit)
+{
+    for (int m = 0; m < sc->num_instances; m++) {
+        const o_instance* mi = &sc->instances[m];
+        const o_mesh* mesh = sc->meshes[mi->mesh_index];
+        ray_t r = instance_ray(mi, origin, direction);
+        for (int i = 0; i < mesh->num_triangles; i++) {
+            const o_tri* tri = &mesh->triangles[i];
+            o_f3 isect; o_f2 uv;
+            if (!tri_ray_intersect(tri, &r, &isect) || !tri_point_inside(tri, isect, &uv)) continue;
+            if (!(dot3(r.direction, tri->normal) < 0)) continue;
+            o_f3 loc = f3(isect.x * mi->scale.x, isect.y * mi->scale.y, isect.z * mi->scale.z);
+            loc = o_apply_lre(mi->inv_pose, loc);
+            float distance = magnitude3(sub3(loc, origin));
+            if (hit->min == FLT_MAX || distance < hit->min) {          /* m, i ascend: a later equal distance never replaces */
+                hit->min = distance;
+                o_f3 nrm = o_apply_euler(mi->inv_rotation, tri->normal);
+                nrm.x *= mi->scale.x; nrm.y *= mi->scale.y; nrm.z *= mi->scale.z;
+                hit->normal = o_normalize(nrm);
+                hit->uv = uv; hit->material = mi->material_index; hit->location = loc;
+                hit->prim = i; hit->inst = m;
+                if (any_hit) return;
+            }
+        }
+    }
+}
+
+int o_cast_ray_exhaustive(const o_scene* sc, o_f3 origin, o_f3 direction, int* prim, int* inst, float* t)
+{
+    float best = FLT_MAX; int bp = -1, bi = -1;
+    for (int m = 0; m < sc->num_instances; m++) {
+        const o_instance* mi = &sc->instances[m];
+        const o_mesh* mesh = sc->meshes[mi->mesh_index];
+        ray_t r = instance_ray(mi, origin, direction);
+        for (int i = 0; i < mesh->num_triangles; i++) {
+            float d;
+            if (candidate(mi, mesh, &r, origin, i, &d) && (best == FLT_MAX || d < best)) { best = d; bp = i; bi = m; }
+        }
+    }
+    *prim = bp; *inst = bi; *t = best;
+    return bp >= 0;
+}
+
 /* raycast.cu:156-188: pixel -> world-space ray direction.  (px,py) are the float pixel coordinates
  * (integers in the reference; the path-tracing extension adds a sub-pixel jitter). */
 static o_f3 generate_direction(const o_render_params* p, float px, float py)
@@ -625,6 +716,13 @@ static o_f3 generate_direction(const o_render_params* p, float px, float py)
     d = o_apply_euler(f3(p->inv_pose.yaw, p->inv_pose.pitch, p->inv_pose.roll), d);
     d = o_normalize(d);
     return d;
+}
+
+/* the camera ray of pixel (x, y) as o_render casts it in the non-jittered modes (raycast.cu:156-188) */
+void o_pixel_ray(const o_render_params* p, int x, int y, o_f3* origin, o_f3* direction)
+{
+    *origin = f3(p->pose.x, p->pose.y, p->pose.z);
+    *direction = generate_direction(p, (float)x, (float)y);
 }
 
 /* raycast.cu:224-245: base colour of the hit (BGR floats) */
@@ -798,6 +896,13 @@ typedef struct {
     int y1; int next_row;           /* next_row: atomic row counter */
     uint64_t rays, nodes, boxes, tris; pthread_mutex_t mu;
 } job_t;
+
+/* one pixel of o_render (test support: re-render single pixels, e.g. with o_set_exhaustive(1)) */
+void o_render_pixel(const o_scene* sc, const o_render_params* p, int x, int y, uint8_t bgr[3], int32_t* prim, int32_t* inst, float* t)
+{
+    uint64_t rays = 0;
+    render_pixel(sc, p, x, y, bgr, prim, inst, t, NULL, &rays);
+}
 
 static void* render_worker(void* arg)
 {

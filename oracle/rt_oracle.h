@@ -114,6 +114,12 @@ void o_render(const o_scene* scene, const o_render_params* p, uint8_t* img, size
 /* single ray closest hit, for unit tests: returns 1 on hit */
 int o_cast_ray(const o_scene* scene, o_f3 origin, o_f3 direction, int* prim, int* inst, float* t,
                o_f3* location, o_f3* normal, o_f2* uv);
+/* parity-report support (see rt_oracle.c): one candidate's verdict, the BVH-free closest hit, a pixel's camera ray */
+int o_candidate(const o_scene* scene, o_f3 origin, o_f3 direction, int inst, int prim, float* distance);
+int o_cast_ray_exhaustive(const o_scene* scene, o_f3 origin, o_f3 direction, int* prim, int* inst, float* t);
+void o_pixel_ray(const o_render_params* p, int x, int y, o_f3* origin, o_f3* direction);
+void o_set_exhaustive(int on);            /* every cast_ray becomes a BVH-free search over all triangles (process-wide) */
+void o_render_pixel(const o_scene* scene, const o_render_params* p, int x, int y, uint8_t bgr[3], int32_t* prim, int32_t* inst, float* t);
 
 #ifdef __cplusplus
 }

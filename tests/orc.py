@@ -100,6 +100,12 @@ class Oracle:
         L.o_free.argtypes = [C.c_void_p]
         L.o_render.argtypes = [C.POINTER(OScene), C.POINTER(ORenderParams), C.c_void_p, C.c_size_t, C.c_void_p,
                                C.c_void_p, C.c_void_p, C.c_int, C.POINTER(OStats)]
+        L.o_candidate.argtypes = [C.POINTER(OScene), OF3, OF3, C.c_int, C.c_int, C.POINTER(C.c_float)]
+        L.o_cast_ray_exhaustive.argtypes = [C.POINTER(OScene), OF3, OF3, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_float)]
+        L.o_pixel_ray.argtypes = [C.POINTER(ORenderParams), C.c_int, C.c_int, C.POINTER(OF3), C.POINTER(OF3)]
+        L.o_set_exhaustive.argtypes = [C.c_int]
+        L.o_render_pixel.argtypes = [C.POINTER(OScene), C.POINTER(ORenderParams), C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int32),
+                                     C.POINTER(C.c_int32), C.POINTER(C.c_float)]
 
     def q_rsqrt(self, x):
         return np.float32(self.lib.o_Q_rsqrt(np.float32(x)))
@@ -203,8 +209,7 @@ class OracleScene:
         self.c = OScene(len(meshes), self._mesh_ptrs, len(self.mats), self.mats.ctypes.data, len(self.insts),
                         self.insts.ctypes.data)
 
-    def render(self, width, height, K, D, pose, mode=MODE_REFERENCE, max_depth=0, spp=1, seed=42, y0=0, y1=0,
-               nthreads=None, aovs=True, stats=False):
+    def params(self, width, height, K, D, pose, mode=MODE_REFERENCE, max_depth=0, spp=1, seed=42, y0=0, y1=0):
         orc = self.orc
         p = ORenderParams()
         p.width, p.height = width, height
@@ -217,6 +222,43 @@ class OracleScene:
         ip = orc.invert_lre(pose)
         p.inv_pose = OLre(*[float(t) for t in ip])
         p.mode, p.max_depth, p.spp, p.seed, p.y0, p.y1 = mode, max_depth, spp, seed, y0, y1 or height
+        return p
+
+    # ---- parity-report support: why does a pixel differ?
+    def pixel_ray(self, width, height, K, D, pose, x, y):
+        p = self.params(width, height, K, D, pose)
+        o, d = OF3(), OF3()
+        self.orc.lib.o_pixel_ray(C.byref(p), int(x), int(y), C.byref(o), C.byref(d))
+        return o, d
+
+    def candidate(self, o, d, inst, prim):
+        """world distance of (inst, prim) along the ray if it passes the reference's accept predicate, else None"""
+        dist = C.c_float()
+        ok = self.orc.lib.o_candidate(C.byref(self.c), o, d, int(inst), int(prim), C.byref(dist))
+        return float(dist.value) if ok else None
+
+    def exhaustive(self, o, d):
+        """(prim, inst, distance) of the closest candidate with no BVH at all"""
+        prim, inst, dist = C.c_int(), C.c_int(), C.c_float()
+        self.orc.lib.o_cast_ray_exhaustive(C.byref(self.c), o, d, C.byref(prim), C.byref(inst), C.byref(dist))
+        return prim.value, inst.value, float(dist.value)
+
+    def render_pixel(self, width, height, K, D, pose, x, y, mode=MODE_REFERENCE, max_depth=0, spp=1, seed=42, exhaustive=False):
+        """one pixel of render(): (bgr uint8[3], prim, inst, t).  exhaustive: with the BVH-free cast_ray (o_set_exhaustive)"""
+        p = self.params(width, height, K, D, pose, mode, max_depth, spp, seed)
+        bgr = np.zeros(3, np.uint8)
+        prim, inst, t = C.c_int32(-1), C.c_int32(-1), C.c_float(0)
+        self.orc.lib.o_set_exhaustive(1 if exhaustive else 0)
+        try:
+            self.orc.lib.o_render_pixel(C.byref(self.c), C.byref(p), int(x), int(y), _vp(bgr), C.byref(prim), C.byref(inst), C.byref(t))
+        finally:
+            self.orc.lib.o_set_exhaustive(0)
+        return bgr, prim.value, inst.value, float(t.value)
+
+    def render(self, width, height, K, D, pose, mode=MODE_REFERENCE, max_depth=0, spp=1, seed=42, y0=0, y1=0,
+               nthreads=None, aovs=True, stats=False):
+        orc = self.orc
+        p = self.params(width, height, K, D, pose, mode, max_depth, spp, seed, y0, y1)
         img = np.zeros((height, width, 3), np.uint8)
         prim = np.full((height, width), -1, np.int32) if aovs else None
         inst = np.full((height, width), -1, np.int32) if aovs else None

@@ -38,23 +38,88 @@ def make_oracle_scene(oracle, meshes, materials, instances):
     return orc.OracleScene(oracle, om, materials, [oracle.build_instance(m, a, p, s) for (m, a, p, s) in instances])
 
 
-def compare(got, ref, what, id_budget=ID_BUDGET, colour_tol=1, check_inst=True):
+REPORT = []            # one record per compare(): written to gpurun_out/parity_r02.json at the end of the module (committed as profiles/parity_r02.json)
+
+
+@pytest.fixture(scope="module", autouse=True)
+def parity_report():
+    yield
+    import json
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    tot = dict(comparisons=len(REPORT), pixels=sum(r["pixels"] for r in REPORT), id_mismatches=sum(r["id_mismatches"] for r in REPORT),
+               unexplained=sum(r["classes"].get("unexplained", 0) for r in REPORT))
+    with open(os.path.join(out, "parity_r02.json"), "w") as f:
+        json.dump(dict(thresholds=dict(id_budget=ID_BUDGET, t_rel=T_REL, colour=1), total=tot, tests=REPORT), f, indent=1)
+
+
+def explain_mismatch(ex, y, x, got, ref):
+    """Why does pixel (y, x) differ in its first-hit id?  ex = dict(osc=oracle scene, W, H, K, D, pose, y0, ...).  Both candidates
+    are put through the reference's own accept predicate for that pixel's camera ray (oracle: o_candidate):
+      tie          both pass with EXACTLY the same computed distance: the reference keeps the first it meets in ITS traversal order,
+                   the product the lowest (instance, triangle) (SURVEY H5);
+      ref-culled   the product's candidate passes and is closer (or the reference reports a miss): the reference's own box tests culled
+                   it -- its slab test compares distances of different spaces and has no rounding slack (SURVEY Q5, H6);
+      unexplained  anything else -- a product bug."""
+    osc = ex["osc"]
+    o, d = osc.pixel_ray(ex["W"], ex["H"], ex["K"], ex["D"], ex["pose"], x, y + ex.get("y0", 0))
+    gp, gi, rp, ri = int(got["prim"][y, x]), int(got["inst"][y, x]), int(ref["prim"][y, x]), int(ref["inst"][y, x])
+    dg = osc.candidate(o, d, gi, gp) if gp >= 0 else None
+    dr = osc.candidate(o, d, ri, rp) if rp >= 0 else None
+    if dg is not None and dr is not None and dg == dr:
+        return "tie"
+    if dg is not None and (dr is None or dg < dr) and np.float32(dg) == got["t"][y, x]:
+        return "ref-culled"
+    return "unexplained"
+
+
+def explain_colour(ex, y, x, got):
+    """A pixel whose first hit agrees but whose colour does not (secondary rays): re-render it in the oracle with the BVH-free
+    cast_ray (o_set_exhaustive: every triangle of every instance, ties to the lowest (instance, triangle)).  If THAT colour is the
+    product's, the difference comes from the reference's own culling / tie order on a secondary ray, not from the product."""
+    bgr, _, _, _ = ex["osc"].render_pixel(ex["W"], ex["H"], ex["K"], ex["D"], ex["pose"], x, y + ex.get("y0", 0), mode=ex.get("mode", 0),
+                                          max_depth=ex.get("max_depth", 0), spp=ex.get("spp", 1), seed=ex.get("seed", 42), exhaustive=True)
+    return "secondary ray: ref-culled or tie" if int(np.abs(bgr.astype(int) - got["img"][y, x].astype(int)).max()) <= 1 else "unexplained"
+
+
+def compare(got, ref, what, id_budget=ID_BUDGET, colour_budget=0.0, check_inst=True, explain=None):
+    """ids: <= id_budget of the pixels may differ and every examined one must be a tie or the reference's own mis-cull;
+    t: 1e-5 relative where the ids agree; colour: 1/255 where the ids agree, except <= colour_budget of the pixels whose difference
+    the BVH-free oracle explains (secondary rays only)."""
     H, W = ref["prim"].shape
     bad = (got["prim"] != ref["prim"])
     if check_inst:
         bad |= (got["inst"] != ref["inst"])
     nbad = int(bad.sum())
-    listing = [(int(y), int(x), int(got["prim"][y, x]), int(ref["prim"][y, x])) for y, x in zip(*np.nonzero(bad))][:20]
-    assert nbad <= max(1, int(id_budget * W * H)), "%s: %d/%d id mismatches (y,x,got,ref): %s" % (what, nbad, W * H, listing)
+    ys, xs = np.nonzero(bad)
+    listing, classes = [], {}
+    for y, x in list(zip(ys.tolist(), xs.tolist()))[:200]:
+        why = explain_mismatch(explain, y, x, got, ref) if explain is not None and len(listing) < 60 else "not examined"
+        classes[why] = classes.get(why, 0) + 1
+        listing.append(dict(y=y, x=x, got=[int(got["inst"][y, x]), int(got["prim"][y, x])], ref=[int(ref["inst"][y, x]), int(ref["prim"][y, x])], why=why))
     same = ~bad
     hit = same & (ref["prim"] >= 0)
-    if hit.any():
-        rel = np.abs(got["t"][hit] - ref["t"][hit]) / ref["t"][hit]
-        assert float(rel.max()) <= T_REL, "%s: max relative t error %.3e" % (what, float(rel.max()))
+    rel = float((np.abs(got["t"][hit] - ref["t"][hit]) / ref["t"][hit]).max()) if hit.any() else 0.0
     miss = same & (ref["prim"] < 0)
+    dc = np.where(same, np.abs(got["img"].astype(int) - ref["img"].astype(int)).max(axis=2), 0)
+    cys, cxs = np.nonzero(dc > 1)
+    clist, cclasses = [], {}
+    for y, x in list(zip(cys.tolist(), cxs.tolist()))[:200]:
+        why = explain_colour(explain, y, x, got) if explain is not None and explain.get("mode", 0) >= 2 and len(clist) < 40 else "not examined"
+        cclasses[why] = cclasses.get(why, 0) + 1
+        clist.append(dict(y=y, x=x, got=got["img"][y, x].tolist(), ref=ref["img"][y, x].tolist(), why=why))
+    rec = dict(test=what, pixels=int(W * H), id_mismatches=nbad, id_fraction=nbad / float(W * H), id_budget=id_budget, classes=classes, listed=listing,
+               max_rel_t=rel, max_colour_diff=int(dc.max()) if dc.size else 0, colour_over_1=int(len(cys)), colour_budget=colour_budget,
+               colour_classes=cclasses, colour_listed=clist)
+    REPORT.append(rec)
+    assert nbad <= max(1, int(id_budget * W * H)), "%s: %d/%d id mismatches: %s" % (what, nbad, W * H, listing[:20])
+    assert classes.get("unexplained", 0) == 0, "%s: mismatches that are neither ties nor the reference's own culling: %s" % (
+        what, [l for l in listing if l["why"] == "unexplained"][:10])
+    assert rel <= T_REL, "%s: max relative t error %.3e" % (what, rel)
     assert np.all(got["t"][miss] == ref["t"][miss]), what + ": miss distance must be FLT_MAX"
-    dc = np.abs(got["img"].astype(int) - ref["img"].astype(int))[same]
-    assert dc.size == 0 or int(dc.max()) <= colour_tol, "%s: colour differs by %d/255" % (what, int(dc.max()))
+    assert len(cys) <= int(colour_budget * W * H), "%s: %d pixels differ by more than 1/255 (max %d): %s" % (what, len(cys), int(dc.max()), clist[:10])
+    assert cclasses.get("unexplained", 0) == 0, "%s: colour differences the BVH-free oracle does not explain: %s" % (
+        what, [l for l in clist if l["why"] == "unexplained"][:10])
     return nbad
 
 
@@ -99,21 +164,23 @@ def test_c1_obj_primary(rtb, oracle, tmp_path, pose, fisheye):
     s = make_rtb_scene(rtb, [mesh.triangles], mats, inst)
     got = render_rtb(rtb, s, 640, 480, synth.C1_K, D, pose)
     s.close()
-    ref = make_oracle_scene(oracle, [tris_o], mats, inst).render(640, 480, synth.C1_K, D, pose)
-    compare(got, ref, "C1 pose %s fisheye %s" % (pose, fisheye))
+    osc = make_oracle_scene(oracle, [tris_o], mats, inst)
+    ref = osc.render(640, 480, synth.C1_K, D, pose)
+    compare(got, ref, "C1 pose %s fisheye %s" % (pose, fisheye), explain=dict(osc=osc, W=640, H=480, K=synth.C1_K, D=D, pose=pose))
 
 
 # ------------------------------------------------------------------ golden fixture generated by the reference itself
-def test_reference_fixture_scene(rtb):
+def test_reference_fixture_scene(rtb, oracle):
     g = np.load(os.path.join(os.path.dirname(__file__), "golden", "render_small.npz"))
     from test_oracle_cpu import GOLD_INSTS
     mats = [dict(albedo=(0.1, 0.2, 0.9)), dict(albedo=(1, 1, 1), texture=g["tex"])]
     # the scaled instance (1.25) exercises the reference's mixed-space pruning quirk; unit-scale ones must be exact
     s = make_rtb_scene(rtb, [g["small"], g["soup"]], mats, GOLD_INSTS)
+    osc = make_oracle_scene(oracle, [g["small"], g["soup"]], mats, GOLD_INSTS)      # only to explain mismatches: `ref` is the reference's output
     for k in range(2):
         got = render_rtb(rtb, s, int(g["W"]), int(g["H"]), g["K"], g["D%d" % k], g["pose%d" % k])
         ref = dict(img=g["img%d" % k], prim=g["prim%d" % k], inst=g["inst%d" % k], t=g["t%d" % k])
-        compare(got, ref, "reference fixture cam %d" % k, id_budget=2e-3)
+        compare(got, ref, "reference fixture cam %d" % k, explain=dict(osc=osc, W=int(g["W"]), H=int(g["H"]), K=g["K"], D=g["D%d" % k], pose=g["pose%d" % k]))
     s.close()
 
 
@@ -142,9 +209,10 @@ def test_instances_textures_shadow(rtb, oracle, mode):
     s = make_rtb_scene(rtb, meshes, mats, insts)
     got = render_rtb(rtb, s, 320, 240, K, synth.REF_D, pose, mode=mode)
     s.close()
-    ref = make_oracle_scene(oracle, meshes, mats, insts).render(320, 240, K, synth.REF_D, pose, mode=mode)
+    osc = make_oracle_scene(oracle, meshes, mats, insts)
+    ref = osc.render(320, 240, K, synth.REF_D, pose, mode=mode)
     assert (ref["inst"] >= 1).mean() > 0.05            # several instances are actually visible
-    compare(got, ref, "instanced mode %d" % mode, id_budget=5e-4)
+    compare(got, ref, "instanced mode %d" % mode, explain=dict(osc=osc, W=320, H=240, K=K, D=synth.REF_D, pose=pose, mode=mode))
 
 
 @pytest.mark.parametrize("fused", [2, 1, 0])
@@ -162,13 +230,14 @@ def test_reflections_wavefront(rtb, oracle, fused):
     finally:
         s.set_option("fused", -1)
         s.close()
-    ref = make_oracle_scene(oracle, meshes, mats, insts).render(320, 240, K, synth.ZERO_D, pose, mode=2, max_depth=4, stats=True)
-    # secondary rays start from rounded hit points: allow a few more colour outliers than for primary rays
-    bad = compare(got, ref, "reflect", id_budget=5e-4, colour_tol=255)
-    dc = np.abs(got["img"].astype(int) - ref["img"].astype(int)).max(axis=2)
-    assert (dc > 1).mean() <= 1e-3, "reflection colours: %.4f%% of pixels differ by more than 1/255" % (100 * (dc > 1).mean())
+    osc = make_oracle_scene(oracle, meshes, mats, insts)
+    ref = osc.render(320, 240, K, synth.ZERO_D, pose, mode=2, max_depth=4, stats=True)
+    # a secondary ray may meet one of the reference's own mis-culls / traversal-order ties: such pixels are few, and each is shown
+    # to carry the colour the reference's accept rule yields without its BVH (explain_colour)
+    compare(got, ref, "reflect fused=%d" % fused, colour_budget=1e-3,
+            explain=dict(osc=osc, W=320, H=240, K=K, D=synth.ZERO_D, pose=pose, mode=2, max_depth=4))
     assert abs(int(st["rays"]) - int(ref["stats"]["rays"])) <= 1e-3 * ref["stats"]["rays"], (st["rays"], ref["stats"]["rays"])
-    assert st["rays"] > 320 * 240 * 1.2 and st["launches"] == (1 if fused else 1 + 3 * 5 + 1)
+    assert st["rays"] > 320 * 240 * 1.2 and st["launches"] == (3 if fused else 1 + 3 * 5 + 1)      # fused: frame begin, the persistent kernel, frame emission
 
 
 @pytest.mark.parametrize("fused", [2, 1, 0])
@@ -183,11 +252,12 @@ def test_path_tracing_wavefront(rtb, oracle, fused):
     finally:
         s.set_option("fused", -1)
         s.close()
-    ref = make_oracle_scene(oracle, meshes, mats, insts).render(160, 120, K, synth.ZERO_D, pose, mode=3, max_depth=3, spp=8, seed=42)
-    compare(got, ref, "path AOVs", id_budget=5e-4, colour_tol=255)          # first-hit AOVs exact
-    # counter-based RNG is shared bit for bit, so almost every pixel is identical; libm-vs-CUDA sinf/cosf may flip a path
-    dc = np.abs(got["img"].astype(int) - ref["img"].astype(int)).max(axis=2)
-    assert (dc > 1).mean() <= 0.02, "path tracing: %.3f%% of pixels off by more than 1/255" % (100 * (dc > 1).mean())
+    osc = make_oracle_scene(oracle, meshes, mats, insts)
+    ref = osc.render(160, 120, K, synth.ZERO_D, pose, mode=3, max_depth=3, spp=8, seed=42)
+    # counter-based RNG and the hemisphere sampling arithmetic are shared bit for bit (no libm on either side), so a pixel differs
+    # only where one of its 8 x 4 rays meets one of the reference's own mis-culls / traversal-order ties
+    compare(got, ref, "path fused=%d" % fused, colour_budget=2e-3,
+            explain=dict(osc=osc, W=160, H=120, K=K, D=synth.ZERO_D, pose=pose, mode=3, max_depth=3, spp=8, seed=42))
     assert abs(got["img"].astype(float).mean() - ref["img"].astype(float).mean()) < 0.5
 
 
