@@ -81,9 +81,9 @@ def config_dict(cfg, name, n_tris):
 
 
 def flops_per_ray(nodes, tris):
-    """SURVEY 8(d)'s arithmetic model restated for the 8-wide compressed node: per node visit 8 children x (6 fma + 4 min/max +
-    3 differences = 19 flops) + 18 for the per-node ray constants; per triangle test 30; 80 per ray for setup and the accept rule."""
-    return nodes * (8 * 19 + 18) + tris * 30 + 80
+    """SURVEY 8(d)'s arithmetic model: per wide-node visit 4 children x 24 flops (6 fma = 12, 6 min/max, compares and the key),
+    per triangle test 30, 80 per ray for setup and the accept rule."""
+    return nodes * 4 * 24 + tris * 30 + 80
 
 
 class ClockSampler(threading.Thread):
@@ -400,7 +400,7 @@ def main():
         nodes_per_ray, tris_per_ray = cnt["nodes"] / max(1, cnt["rays"]), cnt["tris"] / max(1, cnt["rays"])
         rays_f = cnt["rays"] / max(1, n_count)                               # rays per frame of this rank's share
         hops = max(0.0, rays_f - my_pixels * (cfg["spp"] if cfg["mode"] == 3 else 1)) if cfg["mode"] >= 2 else 0.0
-        node_b, tri_b, hop_b = 80, 64, 64                                   # bytes per node visit / triangle test / queue hop (32 written + 32 read)
+        node_b, tri_b, hop_b = 112, 64, 64                                   # bytes per node visit / triangle test / queue hop (32 written + 32 read)
         alg_bytes = rays_f * (nodes_per_ray * node_b + tris_per_ray * tri_b) + my_pixels * 3 + hops * hop_b
         ach = alg_bytes / (kms * 1e-3) / 1e9
         flops = rays_f * flops_per_ray(nodes_per_ray, tris_per_ray)

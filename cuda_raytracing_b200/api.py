@@ -44,21 +44,6 @@ class Aovs(C.Structure):
     _fields_ = [("prim", C.c_void_p), ("inst", C.c_void_p), ("t", C.c_void_p)]
 
 
-# the 80-byte compressed 8-wide node (csrc/rtb_internal.cuh): q[axis][0 = lo, 1 = hi][child] are plane bytes on the grid
-# origin + q * 2^(e - 127 - 15); imask bit k = child k is an inner node (index child_base + popcount(imask below k));
-# meta[k] of a leaf child = 0x80 | (count - 1) << 5 | offset: triangle records tri_base + offset .. + count - 1
-NODE_DT = np.dtype([("origin", "<f4", (3,)), ("e", "u1", (3,)), ("imask", "u1"), ("child_base", "<i4"), ("tri_base", "<i4"),
-                    ("meta", "u1", (8,)), ("q", "u1", (3, 2, 8))])
-assert NODE_DT.itemsize == 80
-
-
-def node_child_boxes(nodes):
-    """Decoded child boxes of NODE_DT records: (lo, hi), each (N, 3, 8) float64 (exact: origin + q * cell)."""
-    cell = np.exp2(nodes["e"].astype(np.float64) - 127 - 15)[:, :, None]
-    org = nodes["origin"].astype(np.float64)[:, :, None]
-    return org + nodes["q"][:, :, 0, :] * cell, org + nodes["q"][:, :, 1, :] * cell
-
-
 class MeshInfo(C.Structure):
     _fields_ = [("num_triangles", C.c_int), ("num_nodes", C.c_int), ("num_leaves", C.c_int),
                 ("max_leaf_size", C.c_int), ("depth", C.c_int), ("stack_need", C.c_int), ("build_ms", C.c_float),
@@ -296,10 +281,9 @@ class Scene:
         return {f: (list(getattr(info, f)) if f.startswith("bounds") else getattr(info, f)) for f, _ in MeshInfo._fields_}
 
     def mesh_arrays(self, index):
-        """Download the wide nodes (N records of NODE_DT, 80 bytes each), triangle records (T,4,4 float32) and the triangle
-        order (T uint32: record slot -> original triangle)."""
+        """Download the wide nodes (N,7,4 float32), triangle records (T,4,4 float32) and leaf order (T uint32)."""
         info = self.mesh_info(index)
-        nodes = np.zeros(info["num_nodes"], NODE_DT)
+        nodes = np.zeros((info["num_nodes"], 7, 4), np.float32)
         tris = np.zeros((info["num_triangles"], 4, 4), np.float32)
         order = np.zeros(info["num_triangles"], np.uint32)
         for what, arr in ((0, nodes), (1, tris), (2, order)):

@@ -212,8 +212,9 @@ struct MeshState {                  // shared by every copy of a MeshPrimitive (
     std::vector<TrianglePrimitive> triangles;
     std::shared_ptr<Context> owner;
     int mesh_id = -1;
+    int replicas = 0;               // devices the BLAS is resident on (Scene::use_devices)
 };
-struct TextureState { std::vector<unsigned char> bgr; int w = 0, h = 0; bool uploaded = false; };
+struct TextureState { std::vector<unsigned char> bgr; int w = 0, h = 0; bool uploaded = false; std::vector<unsigned char*> dev; size_t pitch = 0; };
 inline void die(const char* what)
 {
     std::cerr << what << ": " << rtb_last_error() << std::endl;

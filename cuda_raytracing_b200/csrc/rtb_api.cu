@@ -4,7 +4,6 @@
 #include "rtb_build.cuh"
 #include "rtb_render.cuh"
 #include "rtb_hostmath.h"
-#include "rtb_cwnode.cuh"
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -62,9 +61,10 @@ struct rtb_context {
     unsigned char* frame_d = nullptr; size_t frame_pitch = 0; int frame_w = 0, frame_h = 0;
     int32_t* aov_prim_d = nullptr; int32_t* aov_inst_d = nullptr; float* aov_t_d = nullptr; size_t aov_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t frame_done = nullptr;   // recorded after every rtb_render on its stream: BLAS / TLAS / material updates (stream 0) wait for it
     float last_ms = 0.f;
     int last_launches = 0;
-    int opt_counters = 0, opt_leaf = MAX_LEAF, opt_key_bits = 0;
+    int opt_counters = 0, opt_leaf = 8, opt_key_bits = 0;
     rtb::Tune tune;                // kernel tuning knobs of THIS context (rtb_set_option)
     float sah_node_cost = 1.0f;    // option "sah_node" (permille)
     rtb::LaunchInfo last_info;
@@ -95,6 +95,7 @@ int rtb_context_create(int device, rtb_context** out)
     CU(cudaMemset(c->counters_d, 0, sizeof(Counters)), "cudaMemset counters");
     CU(cudaEventCreate(&c->ev0), "cudaEventCreate");
     CU(cudaEventCreate(&c->ev1), "cudaEventCreate");
+    CU(cudaEventCreateWithFlags(&c->frame_done, cudaEventDisableTiming), "cudaEventCreate");
     *out = c;
     return RTB_OK;
 }
@@ -132,6 +133,7 @@ void rtb_context_destroy(rtb_context* c)
     c->ws.release(); c->stage.release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->frame_done) cudaEventDestroy(c->frame_done);
     delete c;
 }
 
@@ -146,6 +148,7 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     else if (n == "inst_cut") { c->opt_inst_cut = std::max(1, std::min(value, 1024)); c->tlas_dirty = !c->instances_h.empty(); }
     else if (n == "fused") c->tune.fused = value;
     else if (n == "cost_order") c->tune.cost_order = value;
+    else if (n == "cost_block") c->tune.cost_block = std::max(0, std::min(value, 3));
     else if (n == "queue_keep") c->tune.queue_keep = std::max(1, std::min(value, 33));
     else if (n == "tail_idle") c->tune.tail_idle = std::max(1, std::min(value, 32));
     else if (n == "spec_thr") c->tune.spec_thr = std::max(0, std::min(value, 31));
@@ -162,6 +165,7 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
 {
     CU(cudaSetDevice(c->device), "cudaSetDevice");
     cudaStream_t st = 0;
+    CU(cudaStreamWaitEvent(st, c->frame_done, 0), "wait for the frame in flight");   // a frame on a non-blocking stream may still read this BLAS
     const size_t nn = (size_t)(n > 0 ? n : 1);
     c->stage.reset();
     CU(c->stage.reserve(nn * (on_device ? 32 : 32 + sizeof(rtb_triangle)) + 4096), "stage reserve");
@@ -190,7 +194,7 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
     m.n = n; m.alive = true;
     rtb_mesh_info& I = m.info;
     I.num_triangles = n; I.num_nodes = m.bvh.num_nodes; I.num_leaves = m.bvh.num_leaves; I.max_leaf_size = m.bvh.max_leaf;
-    I.depth = m.bvh.depth; I.stack_need = m.bvh.depth + 1; I.build_ms = ms; I.sah_cost = m.bvh.sah;
+    I.depth = m.bvh.depth; I.stack_need = 3 * m.bvh.depth + 2; I.build_ms = ms; I.sah_cost = m.bvh.sah;
     for (int k = 0; k < 3; k++) { I.bounds_min[k] = m.bvh.bounds[k]; I.bounds_max[k] = m.bvh.bounds[k + 3]; }
     I.device_bytes = sizeof(float4) * TRI_F4 * nn + sizeof(float2) * 3 * nn + sizeof(float4) * NODE_F4 * (size_t)m.bvh.node_cap +
                      sizeof(unsigned) * (size_t)m.bvh.order_cap;
@@ -285,6 +289,7 @@ int rtb_set_materials(rtb_context* c, const rtb_material* mats, int n)
 {
     if (!c || n < 0 || (n > 0 && !mats)) return fail(RTB_ERR_INVALID, "rtb_set_materials: bad argument");
     CU(cudaSetDevice(c->device), "cudaSetDevice");
+    CU(cudaStreamWaitEvent(0, c->frame_done, 0), "wait for the frame in flight");
     c->materials_h.assign(mats, mats + n);
     if (c->materials_cap < n || !c->materials_d) {
         if (c->materials_d) cudaFree(c->materials_d);
@@ -315,19 +320,19 @@ static int mesh_cut(rtb_context* c, MeshRec& m, int budget)
         }
         for (int k = 0; k < 3; k++) m.cut.push_back(b[k + 3] + (b[k] - m.cut[k]));
     } else if (m.n > 0 && finite && budget > 1 && m.bvh.num_nodes >= 1) {
-        const int K = std::min(m.bvh.num_nodes, 73);                  // the root and its first two levels at most
+        const int K = std::min(m.bvh.num_nodes, 85);
         std::vector<float4> nd((size_t)K * NODE_F4);
         CU(cudaMemcpy(nd.data(), m.bvh.nodes, sizeof(float4) * nd.size(), cudaMemcpyDeviceToHost), "read top BLAS levels");
-        struct Box { float lo[3], hi[3]; int node; };     // node >= 0: an inner child that may be opened further
+        struct Box { float lo[3], hi[3]; int ref; };
         std::vector<Box> open, done;                      // open: FIFO (head index), so the cut is opened level by level
         auto children = [&](int node) {
-            const CwNodeView v = cw_view(&nd[(size_t)node * NODE_F4]);
-            for (int k = 0; k < 8; k++) {
-                const int kind = cw_child_kind(v, k);
-                if (kind == 0) continue;
+            const float* f = (const float*)&nd[(size_t)node * NODE_F4];
+            for (int k = 0; k < 4; k++) {
+                int ref; memcpy(&ref, f + 24 + k, 4);
+                if (ref == EMPTY_REF) continue;
                 Box x;
-                cw_child_box(v, k, x.lo, x.hi);           // the decoded (quantised, hence conservative) child box
-                x.node = kind == 1 ? cw_child_node(v, k) : -1;
+                for (int a = 0; a < 3; a++) { x.lo[a] = f[8 * a + k]; x.hi[a] = f[8 * a + 4 + k]; }
+                x.ref = ref;
                 open.push_back(x);
             }
         };
@@ -335,7 +340,7 @@ static int mesh_cut(rtb_context* c, MeshRec& m, int budget)
         size_t head = 0;
         while (head < open.size()) {
             const Box x = open[head++];
-            if (x.node >= 0 && x.node < K && done.size() + (open.size() - head) + 8 <= (size_t)budget) children(x.node);
+            if (x.ref >= 0 && x.ref < K && done.size() + (open.size() - head) + 4 <= (size_t)budget) children(x.ref);
             else done.push_back(x);
         }
         for (const Box& x : done)
@@ -405,6 +410,7 @@ static int pack_instance(rtb_context* c, const rtb_instance& in, float4 rec[INST
 // rebuilds the TLAS on the device.
 static int rebuild_tlas(rtb_context* c, int only)
 {
+    CU(cudaStreamWaitEvent(0, c->frame_done, 0), "wait for the frame in flight");   // the uploads below are ordered on stream 0
     const int n = (int)c->instances_h.size();
     const int cap = std::max(n, 1);
     if (c->inst_cap < cap) {
@@ -473,15 +479,17 @@ static int make_scene(rtb_context* c, SceneDev& sc)
     for (const auto& in : c->instances_h)
         if (!c->meshes[in.mesh_index].alive) return fail(RTB_ERR_STATE, "render: an instance refers to a destroyed mesh");
     if (c->tlas_dirty) { int rc = rebuild_tlas(c, (int)c->instances_h.size()); if (rc != RTB_OK) return rc; }   // stale boxes only
-    // Worst-case traversal stack: one group per TLAS level, the sentinel, one group per level of the deepest BLAS in use.
-    // A scene that needs more than the kernels' fixed stack is refused here, never rendered wrong.
+    // Worst-case traversal stack (rtb_trace_state.cuh pushes up to 3 children per wide-node visit): 3 entries per TLAS level, the
+    // sentinel of the instance entered, 3 per level of the deepest BLAS in use.  A scene that needs more than the kernels' fixed
+    // stack is refused here with a clear error -- never rendered wrong, and not only reported by the synchronous render path.
     {
         int deepest = 0;
         for (const auto& in : c->instances_h) deepest = std::max(deepest, c->meshes[in.mesh_index].bvh.depth);
-        const int need = (c->instances_h.size() > 1 ? c->tlas.depth + 1 : 0) + deepest + 1;
+        const int need = (c->instances_h.size() > 1 ? 3 * c->tlas.depth + 1 : 0) + 3 * deepest + 2;
         if (need > STACK_CAP)
             return fail(RTB_ERR_OVERFLOW, "render: the scene's trees need a traversal stack of " + std::to_string(need) + " entries, the kernels have " +
-                                              std::to_string((int)STACK_CAP) + " (a degenerate mesh: many primitives with one centroid?)");
+                                              std::to_string((int)STACK_CAP) + " (BLAS depth " + std::to_string(deepest) + ", TLAS depth " +
+                                              std::to_string(c->tlas.depth) + ": a degenerate mesh -- many primitives with one centroid?)");
     }
     if (c->mesh_table_dirty) {
         const int n = (int)c->meshes.size(), cap = std::max(n, 1);
@@ -550,6 +558,7 @@ static int render_impl(rtb_context* c, const rtb_render_params* p, unsigned char
         CU(launch_wavefront(c->tune, c->last_info, &c->wf, sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st), "wavefront launch");
     }
     c->last_launches = c->last_info.launches;
+    CU(cudaEventRecord(c->frame_done, st), "frame event");
     return RTB_OK;
 }
 

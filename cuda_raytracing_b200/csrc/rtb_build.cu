@@ -8,7 +8,6 @@
 // from the reference's tree.  All stages are HBM-bound streaming kernels.
 #include "rtb_build.cuh"
 #include "rtb_sort.cuh"
-#include "rtb_cwnode.cuh"
 #include <cstdio>
 
 namespace rtb {
@@ -42,8 +41,6 @@ struct BuildCounters {
     int qcount[72];         // collapse work-queue sizes per level
     unsigned bar;           // grid barrier of the collapse kernel
     int top_count;          // nodes handed from k_fit to k_fit_top
-    int tri_cursor;         // next free position of the final (node by node) triangle order
-    int bad_box;            // a node box was not finite / not representable: the build is refused
 };
 
 // ------------------------------------------------------------------ 1. primitive boxes + scene bounds
@@ -53,7 +50,7 @@ __global__ void k_init_counters(BuildCounters* c)
     if (t < 3) { c->bounds[t] = f2ord(FLT_MAX); c->bounds[t + 3] = f2ord(-FLT_MAX); c->cbounds[t] = f2ord(FLT_MAX); c->cbounds[t + 3] = f2ord(-FLT_MAX); }
     if (t == 0) { c->n_wide = 1; c->n_leaves = 0; c->max_leaf = 0; c->max_level = 0; c->sah = 0.f; }
     if (t < 72) c->qcount[t] = 0;
-    if (t == 72) { c->bar = 0u; c->top_count = 0; c->tri_cursor = 0; c->bad_box = 0; }
+    if (t == 72) { c->bar = 0u; c->top_count = 0; }
 }
 
 // Scene and centroid bounds of n boxes: BB_PER boxes per thread (all loads issued before the first use), reduced per warp
@@ -305,22 +302,19 @@ __global__ void __launch_bounds__(256) k_fit_top(const int* __restrict__ top_lis
     }
 }
 
-// ------------------------------------------------------------------ 5. top-down collapse to compressed 8-wide nodes
-// One work item = (binary node to open, wide node index to fill).  Greedy surface-area opening: keep replacing the open
-// slot with the largest half-area by its two children until 8 slots are used.  The node is then encoded (rtb_cwnode.cuh):
-// quantisation frame from the opened node's own box, children placed in the slot whose octant best matches their position
-// relative to the node centre, boxes snapped outwards to 8 bits, inner children numbered contiguously in slot order, the
-// triangles of the leaf children moved to one contiguous run of the final triangle order.
+// ------------------------------------------------------------------ 5. top-down collapse to BVH4
+// One work item = (binary node to open, wide node index to fill).  Greedy surface-area opening: keep
+// replacing the open slot with the largest half-area by its two children until 4 slots are used.
 __device__ __forceinline__ void slot_range(int id, int n, const int2* __restrict__ range, int& first, int& count)
 {
     if (id >= n - 1) { first = id - (n - 1); count = 1; }
     else { int2 r = range[id]; first = r.x; count = r.y - r.x + 1; }
 }
 
-// ONE persistent launch for the whole collapse (the host does not know the depth).  Levels are separated by a grid barrier
-// (every CTA is resident: cooperative launch); a wide node's index is (number of nodes of all earlier levels) + (its position
-// in this level's queue), so one level's nodes -- and the inner children of one node -- are contiguous in memory, and the
-// only atomics are two per warp: the next level's count and the triangle cursor.
+// ONE persistent launch for the whole collapse (it was one launch per level, 70 of them: the host does not know the depth).
+// Levels are separated by a grid barrier (every CTA is resident: the grid is sized from the occupancy query); a wide
+// node's index is (number of nodes of all earlier levels) + (its position in this level's queue), so one level's nodes --
+// and the children of one node -- are contiguous in memory, and the only atomic is one per warp on the next level's count.
 __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned target)
 {
     __syncthreads();
@@ -333,100 +327,21 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned target)
     __syncthreads();
 }
 
-__device__ __forceinline__ int warp_exclusive_scan(int v, int lane, int& total)
-{
-    int pre = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
-    total = __shfl_sync(0xffffffffu, pre, 31);
-    return pre - v;
-}
-
-// Encodes one wide node.  ids[0..ns): the binary nodes (or primitives, id >= n - 1) that become its children; inner[k]: child k
-// is opened further (gets a wide node), else it is a leaf of <= MAX_LEAF primitives.  Returns false when the node's box cannot
-// be represented (non-finite or absurd extents: the build is refused).
-__device__ __forceinline__ bool emit_wide_node(float4* __restrict__ nd, const int* ids, const bool* inner, int ns, int n, float4 bl, float4 bh,
-                                               const int2* __restrict__ range, const float4* __restrict__ nb_min, const float4* __restrict__ nb_max,
-                                               const unsigned* __restrict__ order_in, unsigned* __restrict__ order_out,
-                                               int child_base, int level_start, int2* __restrict__ q_out, int tri_base, int& leaves, int& maxleaf)
-{
-    const float org[3] = { bl.x, bl.y, bl.z }, top[3] = { bh.x, bh.y, bh.z };
-    int e[3];
-    bool ok = true;
-#pragma unroll
-    for (int a = 0; a < 3; a++) { e[a] = cw_axis_exponent(org[a], top[a]); ok = ok && e[a] != 0; }
-    if (!ok) return false;
-    // pass A: slots.  Child c takes the free slot whose sign pattern best matches (centre_c - node centre): bit a of the slot set
-    // = the child lies on the + side of axis a; a ray then visits the slots in descending (slot ^ octinv) order, front to back.
-    unsigned used = 0, imask = 0, slots = 0;
-#pragma unroll
-    for (int c = 0; c < 8; c++) {
-        if (c < ns) {
-            const float4 a4 = nb_min[ids[c]], b4 = nb_max[ids[c]];
-            const float rel[3] = { (a4.x + b4.x) - (bl.x + bh.x), (a4.y + b4.y) - (bl.y + bh.y), (a4.z + b4.z) - (bl.z + bh.z) };
-            int best = 0; float bv = -FLT_MAX;
-#pragma unroll
-            for (int s = 0; s < 8; s++) {
-                const float v = ((s & 1) ? rel[0] : -rel[0]) + ((s & 2) ? rel[1] : -rel[1]) + ((s & 4) ? rel[2] : -rel[2]);
-                if (!((used >> s) & 1u) && (v > bv || bv == -FLT_MAX)) { bv = v; best = s; }
-            }
-            used |= 1u << best; slots |= (unsigned)best << (4 * c);
-            if (inner[c]) imask |= 1u << best;
-        }
-    }
-    // pass B: planes, child numbering, leaf triangles
-    // [axis][lo|hi][children 0-3 | 4-7]; a slot without a child keeps lo = 255 > hi = 0: a box no ray can meet
-    const unsigned F = 0xffffffffu;
-    unsigned q[3][2][2] = { { { F, F }, { 0, 0 } }, { { F, F }, { 0, 0 } }, { { F, F }, { 0, 0 } } };
-    unsigned meta[2] = { 0, 0 };
-    int tri_off = 0;
-#pragma unroll
-    for (int c = 0; c < 8; c++) {
-        if (c < ns) {
-            const int s = (int)((slots >> (4 * c)) & 15u), hw = s >> 2, sh = 8 * (s & 3);
-            const float4 a4 = nb_min[ids[c]], b4 = nb_max[ids[c]];
-            const float lo[3] = { a4.x, a4.y, a4.z }, hi[3] = { b4.x, b4.y, b4.z };
-#pragma unroll
-            for (int a = 0; a < 3; a++) {
-                int ql = 0, qh = 255;
-                if (!cw_quantise(org[a], e[a], lo[a], hi[a], ql, qh)) { ql = 0; qh = 255; ok = ok && (lo[a] >= org[a] && hi[a] <= top[a]); }
-                if (hw) { q[a][0][1] ^= (unsigned)(ql ^ 255) << sh; q[a][1][1] |= (unsigned)qh << sh; }
-                else { q[a][0][0] ^= (unsigned)(ql ^ 255) << sh; q[a][1][0] |= (unsigned)qh << sh; }
-            }
-            if (inner[c]) {
-                const int qi = child_base + __popc(imask & ((1u << s) - 1u));
-                q_out[qi] = make_int2(ids[c], level_start + qi);
-            } else {
-                int first, count; slot_range(ids[c], n, range, first, count);
-                const unsigned mb = 0x80u | ((unsigned)(count - 1) << 5) | (unsigned)tri_off;
-                if (hw) meta[1] |= mb << sh; else meta[0] |= mb << sh;
-                for (int j = 0; j < count; j++) order_out[tri_base + tri_off + j] = order_in[first + j];
-                tri_off += count;
-                leaves++; maxleaf = max(maxleaf, count);
-            }
-        }
-    }
-    const unsigned hdr = (unsigned)e[0] | ((unsigned)e[1] << 8) | ((unsigned)e[2] << 16) | (imask << 24);
-    nd[0] = make_float4(org[0], org[1], org[2], __uint_as_float(hdr));
-    nd[1] = make_float4(__int_as_float(level_start + child_base), __int_as_float(tri_base), __uint_as_float(meta[0]), __uint_as_float(meta[1]));
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-        nd[2 + a] = make_float4(__uint_as_float(q[a][0][0]), __uint_as_float(q[a][0][1]), __uint_as_float(q[a][1][0]), __uint_as_float(q[a][1][1]));
-    return ok;
-}
-
+#ifndef RTB_COLLAPSE_MINB
+#define RTB_COLLAPSE_MINB 7
+#endif
 #ifndef RTB_COLLAPSE_CAP
 #define RTB_COLLAPSE_CAP 8
 #endif
-__global__ void __launch_bounds__(128) k_collapse(int2* __restrict__ q0, int2* __restrict__ q1, int n, const int2* __restrict__ range,
-                                                  const float4* __restrict__ nb_min, const float4* __restrict__ nb_max, const int4* __restrict__ topo,
-                                                  const unsigned* __restrict__ order_in, unsigned* __restrict__ order_out,
+__global__ void __launch_bounds__(128, RTB_COLLAPSE_MINB) k_collapse(int2* __restrict__ q0, int2* __restrict__ q1, int n,
+                                                  const int* __restrict__ left, const int* __restrict__ right,
+                                                  const int2* __restrict__ range, const float4* __restrict__ nb_min,
+                                                  const float4* __restrict__ nb_max, const int4* __restrict__ topo,
                                                   float4* __restrict__ nodes, BuildCounters* c)
 {
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
     int my_leaves = 0, my_maxleaf = 0, level = 0;
-    bool bad = false;
     int start = 0;                                                      // wide nodes of the levels before the next one
     for (; level < 70; level++) {
         const int items = *(volatile int*)&c->qcount[level];
@@ -438,13 +353,12 @@ __global__ void __launch_bounds__(128) k_collapse(int2* __restrict__ q0, int2* _
             const int it = it0 + lane;
             const bool active = it < items;
             int2 item = make_int2(0, 0);
-            int slot[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }; int ns = 0;
+            int slot[4] = { 0, 0, 0, 0 }; int ns = 0;
             // per slot: what the greedy opening needs of its binary node -- (left, right, half area, leaf flag), ONE 16-byte record
-            // written by k_fit; area < 0 = cannot be opened (a primitive, or a subtree the SAH decision made a leaf)
-            int cl[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }, cr[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
-            float area[8] = { -1.f, -1.f, -1.f, -1.f, -1.f, -1.f, -1.f, -1.f };
-            bool inner[8] = { false, false, false, false, false, false, false, false };
-            int kc = 0, kt = 0;
+            // written by k_fit (it was four scattered fetches); area < 0 = cannot be opened
+            int cl[4] = { 0, 0, 0, 0 }, cr[4] = { 0, 0, 0, 0 }; float area[4] = { -1.f, -1.f, -1.f, -1.f };
+            bool inner[4] = { false, false, false, false };
+            int kc = 0;
             if (active) {
                 item = __ldcg(q_in + it);
                 // slot k (a run-time index: written through an unrolled select so the arrays stay in registers)
@@ -452,66 +366,79 @@ __global__ void __launch_bounds__(128) k_collapse(int2* __restrict__ q0, int2* _
                     int l = 0, r = 0; float a = -1.f;
                     if (id < n - 1) { const int4 t = __ldg(topo + id); l = t.x; r = t.y; a = t.w ? -1.f : fmaxf(__int_as_float(t.z), 0.f); }
 #pragma unroll
-                    for (int q = 0; q < 8; q++) if (q == k) { slot[q] = id; cl[q] = l; cr[q] = r; area[q] = a; }
+                    for (int q = 0; q < 4; q++) if (q == k) { slot[q] = id; cl[q] = l; cr[q] = r; area[q] = a; }
                 };
                 const int4 t0 = __ldg(topo + item.x);
                 if (t0.w) { fetch(0, item.x); ns = 1; }                      // whole tree is one leaf (tiny meshes)
                 else { fetch(0, t0.x); fetch(1, t0.y); ns = 2; }
-                while (ns < 8) {
+                while (ns < 4) {
                     int best = -1, l = 0, r = 0; float barea = -1.f;
 #pragma unroll
-                    for (int k = 0; k < 8; k++) if (k < ns && area[k] > barea) { barea = area[k]; best = k; l = cl[k]; r = cr[k]; }
+                    for (int k = 0; k < 4; k++) if (k < ns && area[k] > barea) { barea = area[k]; best = k; l = cl[k]; r = cr[k]; }
                     if (best < 0) break;
                     fetch(best, l);
                     fetch(ns++, r);
                 }
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    inner[k] = k < ns && area[k] >= 0.f;
-                    kc += inner[k] ? 1 : 0;
-                    if (k < ns && !inner[k]) { int f, cnt; slot_range(slot[k], n, range, f, cnt); kt += cnt; }
+                for (int k = 0; k < 4; k++) { inner[k] = k < ns && area[k] >= 0.f; kc += inner[k] ? 1 : 0; }
+            }
+            // next level's queue positions for this warp's interior children: exclusive scan + one atomic
+            int pre = kc;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += v; }
+            const int total = __shfl_sync(0xffffffffu, pre, 31);
+            int base = 0;
+            if (lane == 0 && total) base = atomicAdd(&c->qcount[level + 1], total);
+            base = __shfl_sync(0xffffffffu, base, 0) + pre - kc;
+            if (!active) continue;
+            float lo[3][4], hi[3][4]; int ref[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                if (k < ns) {
+                    int id = slot[k];
+                    float4 a = nb_min[id], b = nb_max[id];
+                    lo[0][k] = a.x; lo[1][k] = a.y; lo[2][k] = a.z; hi[0][k] = b.x; hi[1][k] = b.y; hi[2][k] = b.z;
+                    if (!inner[k]) {
+                        int first, count; slot_range(id, n, range, first, count);
+                        ref[k] = ~((first << 3) | (count - 1));
+                        my_leaves++; my_maxleaf = max(my_maxleaf, count);
+                    } else {
+                        const int qi = base++;
+                        q_out[qi] = make_int2(id, start + qi);
+                        ref[k] = start + qi;
+                    }
+                } else {
+                    // empty slot: lo = hi = +inf can never pass a slab test (an inverted box would: min/max un-invert it)
+                    lo[0][k] = lo[1][k] = lo[2][k] = __int_as_float(0x7f800000);
+                    hi[0][k] = hi[1][k] = hi[2][k] = __int_as_float(0x7f800000);
+                    ref[k] = EMPTY_REF;
                 }
             }
-            // next level's queue positions for this warp's inner children and the triangle run of its leaf children:
-            // two exclusive scans + two atomics per warp
-            int tot_c, tot_t;
-            const int pre_c = warp_exclusive_scan(kc, lane, tot_c), pre_t = warp_exclusive_scan(kt, lane, tot_t);
-            int base_c = 0, base_t = 0;
-            if (lane == 0) {
-                if (tot_c) base_c = atomicAdd(&c->qcount[level + 1], tot_c);
-                if (tot_t) base_t = atomicAdd(&c->tri_cursor, tot_t);
-            }
-            base_c = __shfl_sync(0xffffffffu, base_c, 0) + pre_c;
-            base_t = __shfl_sync(0xffffffffu, base_t, 0) + pre_t;
-            if (!active) continue;
-            const float4 bl = nb_min[item.x], bh = nb_max[item.x];
-            if (!emit_wide_node(nodes + (size_t)item.y * NODE_F4, slot, inner, ns, n, bl, bh, range, nb_min, nb_max, order_in, order_out,
-                                base_c, start, q_out, base_t, my_leaves, my_maxleaf)) bad = true;
+            float4* nd = nodes + (size_t)item.y * NODE_F4;
+            nd[0] = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd[1] = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+            nd[2] = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]); nd[3] = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
+            nd[4] = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd[5] = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+            nd[6] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), __int_as_float(ref[2]), __int_as_float(ref[3]));
         }
         grid_barrier(&c->bar, (unsigned)gridDim.x * (unsigned)(level + 1));
     }
     if (my_leaves) { atomicAdd(&c->n_leaves, my_leaves); atomicMax(&c->max_leaf, my_maxleaf); }
-    if (bad) c->bad_box = 1;
     if (blockIdx.x == 0 && threadIdx.x == 0) { c->max_level = level - 1; c->n_wide = start; }
 }
 
 // n == 0 / n == 1 trees: a root with no child / one single-primitive leaf
-__global__ void k_trivial_root(float4* nodes, const float4* bmin, const float4* bmax, int n, unsigned* order, BuildCounters* c)
+__global__ void k_trivial_root(float4* nodes, const float4* bmin, const float4* bmax, int n)
 {
-    float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
-    if (n == 1) { lo = bmin[0]; hi = bmax[0]; order[0] = 0u; }
-    int e[3] = { cw_axis_exponent(lo.x, hi.x), cw_axis_exponent(lo.y, hi.y), cw_axis_exponent(lo.z, hi.z) };
-    if (!e[0] || !e[1] || !e[2]) { c->bad_box = 1; e[0] = e[1] = e[2] = 1; }
-    unsigned q[3][2] = { { 0, 0 }, { 0, 0 }, { 0, 0 } };
-    const float l3[3] = { lo.x, lo.y, lo.z }, h3[3] = { hi.x, hi.y, hi.z };
-    for (int a = 0; a < 3; a++) { int ql = 0, qh = 255; if (n == 1 && !cw_quantise(l3[a], e[a], l3[a], h3[a], ql, qh)) c->bad_box = 1; q[a][0] = ql; q[a][1] = qh; }
-    nodes[0] = make_float4(lo.x, lo.y, lo.z, __uint_as_float((unsigned)e[0] | ((unsigned)e[1] << 8) | ((unsigned)e[2] << 16)));
-    nodes[1] = make_float4(__int_as_float(1), __int_as_float(0), __uint_as_float(n == 1 ? 0x80u : 0u), __uint_as_float(0u));
-    for (int a = 0; a < 3; a++)             // slot 0 holds the primitive (n == 1); every other slot lo = 255 > hi = 0
-        nodes[2 + a] = make_float4(__uint_as_float(n == 1 ? (0xffffff00u | q[a][0]) : 0xffffffffu), __uint_as_float(0xffffffffu),
-                                   __uint_as_float(n == 1 ? q[a][1] : 0u), __uint_as_float(0u));
+    const float pinf = __int_as_float(0x7f800000);
+    float4 lo = make_float4(pinf, pinf, pinf, pinf), hi = lo;
+    float4 lx = lo, ly = lo, lz = lo, hx = hi, hy = hi, hz = hi;
+    int ref0 = EMPTY_REF;
+    if (n == 1) { lx.x = bmin[0].x; ly.x = bmin[0].y; lz.x = bmin[0].z; hx.x = bmax[0].x; hy.x = bmax[0].y; hz.x = bmax[0].z; ref0 = ~0; }
+    nodes[0] = lx; nodes[1] = hx; nodes[2] = ly; nodes[3] = hy; nodes[4] = lz; nodes[5] = hz;
+    nodes[6] = make_float4(__int_as_float(ref0), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF), __int_as_float(EMPTY_REF));
 }
 
+__global__ void k_iota(unsigned* v, int n) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) v[i] = i; }
 __global__ void k_root_sah(const float4* nb_max, BuildCounters* c) { c->sah = nb_max[0].w; }
 
 // ------------------------------------------------------------------ 6. triangle records
@@ -571,10 +498,10 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     const int g = (n + 255) / 256;
     k_morton<K><<<g, 256, 0, st>>>(bmin, bmax, n, ctr, keys[0], vals[0]);
     int cur = radix_sort_pairs<K>(keys, vals, n, key_bits, hist, st);
-    const unsigned* sorted = vals[cur];                                 // Morton order; out.order becomes the node-by-node order (k_collapse)
+    CK(cudaMemcpyAsync(out.order, vals[cur], sizeof(unsigned) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
     CK(cudaMemsetAsync(visit, 0, sizeof(int) * (size_t)n, st));
-    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, sorted, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, sah_node_cost, 1.0f,
+    k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, sah_node_cost, 1.0f,
                                                                    (int*)q0, ctr);
     k_fit_top<<<148 * 4, 256, 0, st>>>((const int*)q0, ctr, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, sah_node_cost, 1.0f);
     k_root_sah<<<1, 1, 0, st>>>(nb_max, ctr);
@@ -594,8 +521,7 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     // cooperative launch: the driver starts the grid only when every CTA can be resident at once, so the grid barrier cannot
     // deadlock against another persistent kernel (a second context building on another stream, a render in flight)
     float4* nodes_out = out.nodes;
-    unsigned* order_out = out.order;
-    void* args[] = { &q0, &q1, &n, &range, &nb_min, &nb_max, &topo, &sorted, &order_out, &nodes_out, &ctr };
+    void* args[] = { &q0, &q1, &n, &left, &right, &range, &nb_min, &nb_max, &topo, &nodes_out, &ctr };
     CK(cudaLaunchCooperativeKernel((const void*)k_collapse, dim3(std::min(resident, (n + 127) / 128)), dim3(128), args, 0, st));
     return cudaGetLastError();
 }
@@ -632,7 +558,8 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
         else k_scene_bounds<false><<<gb, 256, 0, st>>>(nullptr, bmin, bmax, n, ctr);
     }
     if (n <= 1) {
-        k_trivial_root<<<1, 1, 0, st>>>(out.nodes, bmin, bmax, n, out.order, ctr);
+        k_trivial_root<<<1, 1, 0, st>>>(out.nodes, bmin, bmax, n);
+        if (n == 1) k_iota<<<1, 32, 0, st>>>(out.order, 1);
     } else if (wide_keys) {
         CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 48, sah_node_cost, out, ws, ctr, st));
     } else {
@@ -654,9 +581,7 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
     else {
         out.num_nodes = h.n_wide; out.num_leaves = h.n_leaves; out.max_leaf = h.max_leaf; out.depth = h.max_level + 1; out.sah = h.sah;
         if (h.qcount[70] != 0) return cudaErrorLaunchFailure;      // tree deeper than the level loop: refuse, never truncate
-        if (h.tri_cursor != n) return cudaErrorLaunchFailure;      // every primitive must sit in exactly one leaf
     }
-    if (h.bad_box) return cudaErrorInvalidValue;                   // non-finite or unrepresentable bounds
     return cudaSuccess;
 }
 

@@ -43,7 +43,7 @@ struct MegaState {
     size_t cap = 0, pix_cap = 0;
     int nb_cap = 0;
     // the cost map is only reused when the next frame has the same pixel set
-    int hist_w = 0, hist_h = 0, hist_rank = -1, hist_count = 0, hist_mode = -1;
+    int hist_w = 0, hist_h = 0, hist_rank = -1, hist_count = 0, hist_mode = -1, hist_bs = -1;
 };
 
 // Accepted candidates go straight to the pixel's hit record; shadow rays (any-hit) record nothing.
@@ -76,25 +76,26 @@ XF f3 camera_ray(const FrameParams& P, int x, int y, int sample, bool path)
     return generate_direction(P, px, py);
 }
 
-// Claim order.  The rank-local pixel set is cut into coarse blocks of 8 x 8 warp tiles (64 x 32 pixels, 2048 slots);
-// a claimed slot index is (position of the block in `order`) * 2048 + (tile in block) * 32 + (pixel in tile).  `order`
+// Claim order.  The rank-local pixel set is cut into blocks of 2^bs x 2^bs warp tiles (bs = 3: 64 x 32 pixels, 2048 slots; bs = 0:
+// one 8 x 4 tile); a claimed slot index is (position of the block in `order`) * slots per block + (tile in block) * 32 + (pixel in tile).  `order`
 // lists the blocks by DESCENDING cost of the previous frame (longest-processing-time-first: the expensive pixels start
 // early, the cheap ones fill the end of the frame, so the tail of the one persistent launch is short); the cost of a
 // block is the number of traversal rounds its pixels took, accumulated by this kernel for the next frame.
 struct MegaGeo {
     int tiles_x, tile_rows, nbx, nb, n_slots;
+    int bs;                         // a claim block is 2^bs x 2^bs warp tiles (option "cost_block")
     const int* order;               // nb entries or nullptr (identity)
     unsigned* cost;                 // nb entries, accumulated this frame
 };
-constexpr int BLK_SLOTS = 2048;
 
 XF bool slot_to_pixel(const FrameParams& P, const MegaGeo& G, int idx, int& x, int& y, int& blk)
 {
-    const int k = idx >> 11, o = idx & (BLK_SLOTS - 1);
+    const int sh = 5 + 2 * G.bs;
+    const int k = idx >> sh, o = idx & ((1 << sh) - 1);
     blk = G.order ? __ldg(G.order + k) : k;
     const int bx = blk % G.nbx, by = blk / G.nbx;
     const int t = o >> 5, l = o & 31;
-    const int tx = bx * 8 + (t & 7), ty = by * 8 + (t >> 3);
+    const int tx = (bx << G.bs) + (t & ((1 << G.bs) - 1)), ty = (by << G.bs) + (t >> G.bs);
     x = tx * 8 + (l & 7);
     const int yl = ty * 4 + (l >> 3);
     const int band = (yl / BAND_ROWS) * P.tile_count + P.tile_rank;
@@ -246,7 +247,6 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
     TopLevels T;
     T.n_tlas = T.n_blas = 0; T.s_tlas = T.s_blas = T.g_blas = nullptr;
     if (SMEM) stage_top_levels(sc, s_top, T);
-    init_pick_lut();
     RTB_DECL_STACK(stk);
     TraceState S;
     MegaSink sink;
@@ -277,7 +277,8 @@ __global__ void __launch_bounds__(128, MINB) k_mega(int refill_idle, int tail_id
                 const float scale = PATH ? 1.0f / (float)P.spp : 1.0f;
                 B.pix[(size_t)y * P.width + x] = (unsigned)to_u8(xm(clamp01(xm(acc.x, scale)), 255.0f)) | ((unsigned)to_u8(xm(clamp01(xm(acc.y, scale)), 255.0f)) << 8) |
                                                  ((unsigned)to_u8(xm(clamp01(xm(acc.z, scale)), 255.0f)) << 16);
-                if ((idx & 7) == 0) atomicAdd(G.cost + blk, steps);       // 1 pixel in 8 reports: the map is a heuristic, the atomics are not free
+                // 1 pixel in 8 reports when a block is many tiles: the map is a heuristic, same-address atomics are not free
+                if (G.bs == 0 || (idx & 7) == 0) atomicAdd(G.cost + blk, steps);
                 idx = -1;
             }
         }
@@ -380,7 +381,6 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
     const f3 L = mk3(P.light_dir.x, P.light_dir.y, P.light_dir.z);
     TopLevels T;
     T.n_tlas = T.n_blas = 0; T.s_tlas = T.s_blas = T.g_blas = nullptr;
-    init_pick_lut();
     RTB_DECL_STACK(stk);
     TraceState S;
     MegaSink sink;
@@ -557,9 +557,11 @@ cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const 
     MegaGeo G;
     G.tiles_x = (P.width + 7) / 8;
     G.tile_rows = my_bands * (BAND_ROWS / 4);
-    G.nbx = (G.tiles_x + 7) / 8;
-    G.nb = G.nbx * ((G.tile_rows + 7) / 8);
-    G.n_slots = G.nb * BLK_SLOTS;
+    G.bs = std::max(0, std::min(tune.cost_block, 3));
+    const int bt = 1 << G.bs;
+    G.nbx = (G.tiles_x + bt - 1) / bt;
+    G.nb = G.nbx * ((G.tile_rows + bt - 1) / bt);
+    G.n_slots = G.nb * (32 << (2 * G.bs));
     if (P.max_depth > 126 || P.spp >= (1 << 24) || G.nb > (1 << 20)) return cudaErrorInvalidValue;
     if (m->cap < (size_t)G.n_slots || m->nb_cap < G.nb) {
         mega_free(m);
@@ -580,14 +582,14 @@ cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const 
     // 2.1 M slots 3.10 vs 2.86 ms) and always for path tracing, whose chains run for spp samples (C4 at 1/8: 9.3 vs 10.3 ms).
     const int variant = tune.fused >= 0 ? tune.fused : (path || G.n_slots >= 3000000 ? 2 : 1);
     const bool have_hist = variant == 1 && tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
-                           m->hist_count == P.tile_count && m->hist_mode == P.mode;
+                           m->hist_count == P.tile_count && m->hist_mode == P.mode && m->hist_bs == G.bs;
     info.launches = 0; info.variant = variant;
     if (have_hist) { k_order<<<1, 1024, 0, st>>>(m->cost, G.nb, m->order); info.launches = 1; }
     else MCK(cudaMemsetAsync(m->cost, 0, sizeof(unsigned) * (size_t)G.nb, st));
     G.order = have_hist ? m->order : nullptr;
     G.cost = m->cost;
     m->hist_w = variant == 1 ? P.width : 0;                              // the queue variant keeps no cost map
-    m->hist_h = P.height; m->hist_rank = P.tile_rank; m->hist_count = P.tile_count; m->hist_mode = P.mode;
+    m->hist_h = P.height; m->hist_rank = P.tile_rank; m->hist_count = P.tile_count; m->hist_mode = P.mode; m->hist_bs = G.bs;
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

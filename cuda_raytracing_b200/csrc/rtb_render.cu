@@ -20,7 +20,6 @@ __global__ void __launch_bounds__(128, MINB) k_render_direct(SceneDev sc, FrameP
                                                       int32_t* __restrict__ aov_prim, int32_t* __restrict__ aov_inst,
                                                       float* __restrict__ aov_t, Counters* ctr)
 {
-    init_pick_lut();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const int band = blockIdx.y * P.tile_count + P.tile_rank;

@@ -1,63 +1,51 @@
 // rtb_trace_state.cuh -- per-lane traversal state machine (included by rtb_trace.cuh).
 //
-// One ray per lane.  The lane walks compressed 8-wide nodes (rtb_internal.cuh).  What it still has to look at of a node is a
-// GROUP: (first inner child, node index, 8-bit mask of the children its box test let through, their entry parameters as
-// bf16).  The next child is the one whose slot maximises slot ^ octinv -- the builder put every child in the slot whose
-// octant matches its position, so this is front to back without a sort (one lookup in a 2 KB shared-memory table) -- and it
-// is skipped when its entry parameter is no longer below tmax.  When the lane descends and the group still has children
-// it goes to the stack: ONE 32-byte entry per level instead of one entry per child.
+// One ray per lane.  `cur` is the node being visited: >= 0 interior, < 0 an EVENT: a leaf, LEAVE_REF (the
+// sentinel pushed when an instance was entered: "back to world space") or EMPTY_REF (no ray / finished).
+// advance() = "walk interior nodes until this lane holds an event, then handle that event".
+// Control flow is strictly structured (while / if, no goto) so the warp reconverges after every advance():
+// lanes first walk interior nodes until each holds an event, then all lanes handle their events together.
+// The interior loop contains nothing but box tests, the 4-key sort, pushes and a cull-only pop; every
+// space change (enter / leave an instance) is an event, so it never serialises the interior loop.
 //
-// `cur` says what the lane does next: WALK (pick the next child), EMPTY_REF (no ray / finished) or an EVENT: TRIS (two
-// triangle leaves are waiting), ENTER (a TLAS leaf = instance was picked), LEAVE (the sentinel pushed when an instance was
-// entered came off the stack: back to world space).  advance() = "walk until this lane holds an event, then handle it".
-// Control flow is strictly structured (while / if, no goto) so the warp reconverges after every advance(): lanes first
-// walk until each holds an event, then all lanes handle their events together.  Every space change (enter / leave an
-// instance) is an event, so it never serialises the walk.
-//
-// The state is scalars only -- the traversal stack is a separate array handed in by pointer -- so that the whole state
-// lives in registers (an array member with a dynamic index pins the entire struct to local memory).  What is only needed
-// when a candidate passes the inside test (instance inverse pose, scale) is re-read from the 96-byte instance record at
-// that point instead of being carried in registers through the traversal.
+// The state is scalars only -- the traversal stack is a separate array handed in by pointer -- so that the
+// whole state lives in registers (an array member with a dynamic index pins the entire struct to local memory).
+// What is only needed when a candidate passes the inside test (instance inverse pose, scale) is re-read from
+// the 96-byte instance record at that point instead of being carried in registers through the traversal.
 //
 // Two drivers use it:
 //   * trace<>()            one ray to completion (direct kernel, modes 0/1);
-//   * persistent kernels   that refill finished lanes (rtb_wavefront.cu, rtb_mega.cu).
+//   * k_trace_queue<>      persistent warps that refill finished lanes from a ray queue (wavefront, rtb_wavefront.cu).
 #pragma once
 
 namespace rtb {
 
-constexpr int WALK = 0;
-constexpr int EV_TRIS = 1, EV_ENTER = 2, EV_LEAVE = 3;
-constexpr unsigned NO_LEAF = 0xffffffffu;
+constexpr int LEAVE_REF = (int)0x80000001;     // sentinel stack entry: instance exhausted, restore the world-space ray
 
-// Traversal stack of 32-byte group entries in local memory: a = (first inner child, node, cand | imask << 8, -), b = entry
-// parameters; the sentinel has node = 0xffffffff.
+// Traversal stack of (tnear bits, ref) entries.  Default: a per-thread local-memory array.  With -DRTB_SMEM_STACK the
+// first SMEM_STACK_DEPTH entries live in shared memory (column of this thread, stride = 128 threads, conflict-free for
+// lanes at the same depth) and only deeper entries spill to local memory.
+constexpr int SMEM_STACK_DEPTH = 12;
 struct Stack {
-    uint4 a[STACK_CAP], b[STACK_CAP];
+#ifdef RTB_SMEM_STACK
+    uint2* sm;
+    uint2 loc[STACK_CAP - SMEM_STACK_DEPTH];
+    XF void put(int i, uint2 v) { if (i < SMEM_STACK_DEPTH) sm[i * 128] = v; else loc[i - SMEM_STACK_DEPTH] = v; }
+    XF uint2 get(int i) const { return i < SMEM_STACK_DEPTH ? sm[i * 128] : loc[i - SMEM_STACK_DEPTH]; }
+#else
+    uint2 loc[STACK_CAP];
+    XF void put(int i, uint2 v) { loc[i] = v; }
+    XF uint2 get(int i) const { return loc[i]; }
+#endif
 };
+#ifdef RTB_SMEM_STACK
+#define RTB_DECL_STACK(name) __shared__ uint2 name##_sm[SMEM_STACK_DEPTH * 128]; Stack name; name.sm = name##_sm + threadIdx.x
+#else
 #define RTB_DECL_STACK(name) Stack name
+#endif
 
-// Child order table: pick[octinv << 8 | mask] = the set bit k of mask with the largest k ^ octinv (0 for an empty mask).
-// 2 KB of static shared memory per CTA; every kernel that traces calls init_pick_lut() once, before its first ray.
-XF unsigned char* pick_lut()
-{
-    __shared__ unsigned char lut[8 * 256];
-    return lut;
-}
-XF void init_pick_lut()
-{
-    unsigned char* L = pick_lut();
-    for (int i = threadIdx.x; i < 8 * 256; i += blockDim.x) {
-        const int o = i >> 8, m = i & 255;
-        int best = 0, bp = -1;
-        for (int k = 0; k < 8; k++) if (((m >> k) & 1) && (k ^ o) > bp) { bp = k ^ o; best = k; }
-        L[i] = (unsigned char)best;
-    }
-    __syncthreads();
-}
-
-// Hit record kept in registers (direct kernel).  The persistent kernels use a sink that writes accepted candidates
-// straight to the pixel's hit record in HBM and keeps only what the accept rule compares (rtb_mega.cu, rtb_wavefront.cu).
+// Hit record kept in registers (direct kernel).  The queue tracer uses a sink that writes accepted candidates
+// straight to the hit queue in HBM and keeps only what the accept rule compares (rtb_wavefront.cu).
 struct RegSink {
     Hit hit;
     XF void reset() { hit.min = FLT_MAX; hit.slot = -1; hit.prim = -1; hit.inst = -1; hit.u = 0.f; hit.v = 0.f; hit.loc = mk3(0.f, 0.f, 0.f); }
@@ -77,16 +65,12 @@ struct TraceState {
     float inv_len, tmax, tslack;
     const float4* nodes;
     const float4* tris;
-    unsigned g_cb, g_pn, g_hm, g_t01, g_t23, g_t45, g_t67;     // current group
     int cur, sp, cur_inst;
     bool in_blas;
     unsigned n_nodes, n_tris, guard;
     bool overflow;
 
-    XF void clear() { cur = EMPTY_REF; sp = 0; n_nodes = n_tris = guard = 0; overflow = false; in_blas = false; cur_inst = -1; g_hm = 0; }
-
-    // the group "child 0 of nothing": picking it visits node 0 of the current node array
-    XF void root_group() { g_cb = 0u; g_pn = 0u; g_hm = 1u | (1u << 8); g_t01 = g_t23 = g_t45 = g_t67 = 0u; }
+    XF void clear() { cur = EMPTY_REF; sp = 0; n_nodes = n_tris = guard = 0; overflow = false; in_blas = false; cur_inst = -1; }
 
     // raycast.cu:33-45: r_dir = apply_euler(rotation, dir) * inv_scale ; r_org = apply_lre(pose, org) * inv_scale
     XF void enter_instance(const SceneDev& sc, int inst, Stack& stk, bool sentinel)
@@ -97,13 +81,12 @@ struct TraceState {
         cur_inst = inst;
         r.d = xmul3(xapply_quat(q_pose, dir), inv_scale);
         r.o = xmul3(xapply_quat(q_pose, xsub(org, mk3(b.x, b.y, b.z))), inv_scale);
+        setup_slabs(r);
         const MeshDev* m = sc.meshes + __float_as_int(b.w);
-        setup_slabs(r, m->extent);
         nodes = m->nodes; tris = m->tris;
         in_blas = true;
-        if (sentinel) { stk.a[sp] = make_uint4(0u, 0xffffffffu, 0u, 0u); sp++; }
-        root_group();
-        cur = WALK;
+        if (sentinel) stk.put(sp++, make_uint2(0xbf800000u /* -1.0f: never culled */, (unsigned)LEAVE_REF));
+        cur = 0;                                // BLAS root
     }
 
     XF void begin(const SceneDev& sc, f3 o, f3 d, Stack& stk)
@@ -112,7 +95,7 @@ struct TraceState {
         sp = 0; in_blas = false; cur_inst = -1;
         // parametric bound: Euclidean distance = t * |d_world| for every instance (scale cancels), so a subtree entered
         // at t can only hold hits farther than t*|d|.  Slack covers the reference's inverse-pose round-trip error,
-        // which grows with the magnitude of the coordinates involved, not with the distance.
+        // which grows with the magnitude of the coordinates involved (scene extent, ray origin), not with the distance.
         const float il = rsqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
         inv_len = 1.0002f * il;
         tslack = (1e-3f + 1.2e-6f * (sc.tlas_extent + fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)))) * il;
@@ -121,36 +104,28 @@ struct TraceState {
             enter_instance(sc, 0, stk, false);
         } else {
             r.o = o; r.d = d;
-            setup_slabs(r, sc.tlas_extent);
+            setup_slabs(r);
             nodes = sc.tlas_nodes; tris = nullptr;
-            root_group();
-            cur = WALK;
+            cur = 0;                            // TLAS root
         }
     }
 
-    // node i of the current array (SMEM: from the staged copy when it is among the top levels, rtb_tma.cuh)
-    template <bool SMEM>
-    XF const float4* node_ptr(unsigned i, const TopLevels& T) const
+    XF int pop(Stack& stk)
     {
-        const float4* np = nodes + (size_t)i * NODE_F4;
-        if (SMEM) {
-            if (!in_blas) { if ((int)i < T.n_tlas) np = T.s_tlas + i * NODE_F4; }
-            else if ((int)i < T.n_blas && nodes == T.g_blas) np = T.s_blas + i * NODE_F4;
+        while (sp > 0) {
+            const uint2 e = stk.get(--sp);
+            if (__uint_as_float(e.x) < tmax) return (int)e.y;
         }
-        return np;
+        return EMPTY_REF;
     }
 
-    // leaf child k of node pn -> first << 3 | count - 1, or NO_LEAF for a slot that holds no leaf (an empty slot whose
-    // inverted box let the ray through: possible only when the rounding slack exceeds the node, i.e. far away from it)
-    template <bool SMEM>
-    XF unsigned leaf_ref(unsigned pn, unsigned k, const TopLevels& T) const
+    // ref of the child in slot s (0..3) of a node, branch-free (three selects)
+    static XF int sel4(unsigned s, const int4& r)
     {
-        const float4 n1 = node_ld<SMEM>(node_ptr<SMEM>(pn, T) + 1);
-        const unsigned w = (k & 4u) ? __float_as_uint(n1.w) : __float_as_uint(n1.z);
-        const unsigned mb = (w >> (8u * (k & 3u))) & 0xffu;
-        const unsigned first = (unsigned)__float_as_int(n1.y) + (mb & 31u), count = (mb >> 5) & 3u;
-        return (mb & 0x80u) ? ((first << 3) | count) : NO_LEAF;
+        const int lo = (s & 1u) ? r.y : r.x, hi = (s & 1u) ? r.w : r.z;
+        return (s & 2u) ? hi : lo;
     }
+    static XF bool is_leaf_ref(int ref) { return (unsigned)ref > (unsigned)LEAVE_REF; }   // negative, not EMPTY / LEAVE
 
     template <bool ANY, bool COUNT, class Sink>
     XF void advance(const SceneDev& sc, Stack& stk, Sink& sink)
@@ -164,78 +139,58 @@ struct TraceState {
     XF void advance(const SceneDev& sc, Stack& stk, Sink& sink, const TopLevels& T)
     {
         if (++guard > (1u << 22)) { overflow = true; cur = EMPTY_REF; }   // a frame can never hang the device
-        const unsigned char* lut = pick_lut();
-        // Speculative traversal: the first triangle leaf a lane picks is postponed (`pend`) and the lane keeps walking, so it
-        // does useful work while the slower lanes of the warp are still descending; the walk ends for the warp when (almost)
-        // every lane still walking holds a postponed leaf.  Leaves are remembered as (node << 3 | slot); their triangle range is
-        // read from the node's meta word in the triangle phase, so the walk contains ONE kind of load: the node fetch.
-        // All 32 lanes stay in the loop until the warp leaves it together (a full-mask ballot): lanes that took a short path
-        // through the pick phase -- a culled child, a pop -- must not run ahead of the others, or the box test below ends up
-        // executing a few lanes wide (measured: 5.8 lanes, profiles/r03a).
-        unsigned pend = NO_LEAF, leaf = NO_LEAF;
-        for (;;) {
-            int child = -1;
-            if (cur == WALK) {
-#pragma unroll 1
-                for (int tries = 0; tries < 3; tries++) {
-                    if ((g_hm & 0xffu) == 0u) {             // group exhausted: the next one comes off the stack
-                        if (sp == 0) { cur = EMPTY_REF; break; }
-                        sp--;
-                        const uint4 a = stk.a[sp];
-                        if (a.y == 0xffffffffu) { cur = EV_LEAVE; break; }
-                        const uint4 b = stk.b[sp];
-                        g_cb = a.x; g_pn = a.y; g_hm = a.z; g_t01 = b.x; g_t23 = b.y; g_t45 = b.z; g_t67 = b.w;
-                    }
-                    const unsigned k = lut[(r.octinv << 8) | (g_hm & 0xffu)];
-                    g_hm &= ~(1u << k);
-                    const unsigned tw = (k & 4u) ? ((k & 2u) ? g_t67 : g_t45) : ((k & 2u) ? g_t23 : g_t01);
-                    const float tnk = __uint_as_float((k & 1u) ? (tw & 0xffff0000u) : (tw << 16));
-                    if (tnk < tmax) {                       // else: a closer hit was found since the box test (cull only)
-                        if ((g_hm >> (8u + k)) & 1u) { child = (int)(g_cb + __popc((g_hm >> 8) & ((1u << k) - 1u))); break; }
-                        const unsigned id = (g_pn << 3) | k;    // leaf child: triangles (BLAS) or one instance (TLAS)
-                        if (!in_blas) { leaf = id; cur = EV_ENTER; break; }
-                        if (pend == NO_LEAF) pend = id;
-                        else { leaf = id; cur = EV_TRIS; break; }
-                    }
-                }
+        // Speculative traversal: the first triangle leaf a lane meets is postponed (`pend`) and the lane keeps walking
+        // interior nodes, so it does useful work while the slower lanes of the warp are still descending; the loop
+        // ends for the warp when every lane still in it holds a postponed leaf.
+        int pend = EMPTY_REF;
+        while (cur >= 0) {                      // interior nodes
+            unsigned k[4]; int4 refs;
+            if (COUNT) n_nodes++;
+            if (sp + 3 > STACK_CAP) { overflow = true; cur = EMPTY_REF; break; }
+            const float4* np = nodes + (size_t)cur * NODE_F4;
+            if (SMEM) {
+                if (!in_blas) { if (cur < T.n_tlas) np = T.s_tlas + cur * NODE_F4; }
+                else if (cur < T.n_blas && nodes == T.g_blas) np = T.s_blas + cur * NODE_F4;
             }
-            __syncwarp();
-            if (child >= 0) {
-                if (g_hm & 0xffu) {
-                    if (sp >= STACK_CAP) { overflow = true; cur = EMPTY_REF; child = -1; }
-                    else {
-                        stk.a[sp] = make_uint4(g_cb, g_pn, g_hm, 0u);
-                        stk.b[sp] = make_uint4(g_t01, g_t23, g_t45, g_t67);
-                        sp++;
-                    }
-                }
-            }
-            if (child >= 0) {
-                if (COUNT) n_nodes++;
-                const float4* np = node_ptr<SMEM>((unsigned)child, T);
-                const float4 n0 = node_ld<SMEM>(np);
-                const unsigned cb = SMEM ? *(const unsigned*)(np + 1) : __ldg((const unsigned*)(np + 1));
-                NodeHits H;
-                test_node8<SMEM>(np, n0, r, tmax, H);
-                g_cb = cb; g_pn = (unsigned)child;
-                g_hm = H.hits | ((__float_as_uint(n0.w) >> 24) << 8);
-                g_t01 = H.tn01; g_t23 = H.tn23; g_t45 = H.tn45; g_t67 = H.tn67;
-            }
-            if (__popc(__ballot_sync(0xffffffffu, cur == WALK && pend == NO_LEAF)) <= sc.spec_thr) break;
+            test_node<SMEM>(np, r, tmax, k, refs);
+#ifdef RTB_NEAREST_ONLY
+            // A/B variant, measured SLOWER and therefore off (C3 8.17 -> 8.57 ms, same image; profiles/r01f_ab_experiments.txt): only
+            // the nearest child is singled out; the other hit children are pushed in SLOT order -- no sorting network, no ref
+            // selects for them (tools/bvh_lab.py: +3.5 % node visits for hitting rays).  Every entry carries its own entry
+            // distance, so the pop still culls.
+            const unsigned kmin = min(min(k[0], k[1]), min(k[2], k[3]));      // keys are distinct (slot in the low bits) unless all miss
+            if (k[0] != kmin && k[0] != 0xffffffffu) stk.put(sp++, make_uint2(k[0] & ~3u, (unsigned)refs.x));
+            if (k[1] != kmin && k[1] != 0xffffffffu) stk.put(sp++, make_uint2(k[1] & ~3u, (unsigned)refs.y));
+            if (k[2] != kmin && k[2] != 0xffffffffu) stk.put(sp++, make_uint2(k[2] & ~3u, (unsigned)refs.z));
+            if (k[3] != kmin && k[3] != 0xffffffffu) stk.put(sp++, make_uint2(k[3] & ~3u, (unsigned)refs.w));
+            int nxt = sel4(kmin & 3u, refs);
+            if (kmin == 0xffffffffu) nxt = pop(stk);
+#else
+            RTB_CSWAP(k[0], k[1]); RTB_CSWAP(k[2], k[3]); RTB_CSWAP(k[0], k[2]); RTB_CSWAP(k[1], k[3]); RTB_CSWAP(k[1], k[2]);
+            const int c0 = sel4(k[0] & 3u, refs), c1 = sel4(k[1] & 3u, refs), c2 = sel4(k[2] & 3u, refs), c3 = sel4(k[3] & 3u, refs);
+            // far first, so the nearer children are popped first (misses sort last: key 0xffffffff)
+            if (k[3] != 0xffffffffu) stk.put(sp++, make_uint2(k[3] & ~3u, (unsigned)c3));
+            if (k[2] != 0xffffffffu) stk.put(sp++, make_uint2(k[2] & ~3u, (unsigned)c2));
+            if (k[1] != 0xffffffffu) stk.put(sp++, make_uint2(k[1] & ~3u, (unsigned)c1));
+            int nxt = c0;
+            if (k[0] == 0xffffffffu) nxt = pop(stk);
+#endif
+            if (in_blas && pend == EMPTY_REF && is_leaf_ref(nxt)) { pend = nxt; nxt = pop(stk); }
+            cur = nxt;
+            if (__popc(__ballot_sync(__activemask(), pend == EMPTY_REF)) <= sc.spec_thr) break;
         }
-        // triangle ranges of the (up to two) leaves: meta byte of the slot in its node
+        // Reconvergence point: every lane of the warp calls advance() (both drivers guarantee it), and without this
+        // barrier lanes leave the interior loop in small groups and run the leaf code 2 lanes wide (ncu, profiles/r01b).
+        __syncwarp();
+        // triangle phase: the postponed leaf, then the leaf in `cur` (flattened into one loop over triangle slots)
+        const bool cur_leaf = in_blas && is_leaf_ref(cur);
         int t0 = 0, t1 = 0, u0 = 0, u1 = 0;
-        if (pend != NO_LEAF) {
-            const unsigned ref = leaf_ref<SMEM>(pend >> 3, pend & 7u, T);
-            if (ref != NO_LEAF) { t0 = (int)(ref >> 3); t1 = t0 + (int)(ref & 7u) + 1; }
+        if (pend != EMPTY_REF) { const unsigned b = ~(unsigned)pend; t0 = (int)(b >> 3); t1 = t0 + (int)(b & 7u) + 1; }
+        if (cur_leaf) {
+            const unsigned b = ~(unsigned)cur;
+            const int f = (int)(b >> 3), e = f + (int)(b & 7u) + 1;
+            if (pend != EMPTY_REF) { u0 = f; u1 = e; } else { t0 = f; t1 = e; }
         }
-        if (cur == EV_TRIS) {
-            const unsigned ref = leaf_ref<SMEM>(leaf >> 3, leaf & 7u, T);
-            if (ref != NO_LEAF) { u0 = (int)(ref >> 3); u1 = u0 + (int)(ref & 7u) + 1; }
-            if (t0 == t1) { t0 = u0; t1 = u1; u0 = u1 = 0; }
-            cur = WALK;
-        }
-        // triangle phase: the postponed leaf, then the second one (flattened into one loop over triangle slots)
         bool found = false;
         while (t0 < t1) {
             const int slot = t0;
@@ -279,23 +234,16 @@ struct TraceState {
             }
         }
         if ((ANY || sink.any_hit()) && found) { cur = EMPTY_REF; return; }
+        if (cur_leaf) cur = pop(stk);
         // events: leave the instance (sentinel popped), enter the instance of a TLAS leaf
-        if (cur == EV_LEAVE) {                  // instance exhausted: back to world space
+        if (cur == LEAVE_REF) {                 // instance exhausted: back to world space
             in_blas = false; nodes = sc.tlas_nodes;
-            r.o = org; r.d = dir;
-            setup_slabs(r, sc.tlas_extent);
-            g_hm = 0u;
-            cur = WALK;
-        } else if (cur == EV_ENTER) {           // TLAS leaf: exactly one instance slot
-            const unsigned ref = leaf_ref<SMEM>(leaf >> 3, leaf & 7u, T);
-            if (ref == NO_LEAF) { cur = WALK; return; }
-            const int first = (int)(ref >> 3);
-            if (sp + 2 > STACK_CAP) { overflow = true; cur = EMPTY_REF; return; }
-            if (g_hm & 0xffu) {
-                stk.a[sp] = make_uint4(g_cb, g_pn, g_hm, 0u);
-                stk.b[sp] = make_uint4(g_t01, g_t23, g_t45, g_t67);
-                sp++;
-            }
+            cur = pop(stk);
+            if (cur >= 0) { r.o = org; r.d = dir; setup_slabs(r); }
+        }
+        if (!in_blas && is_leaf_ref(cur)) {     // TLAS leaf: exactly one instance slot
+            const int first = (int)((~(unsigned)cur) >> 3);
+            if (sp + 1 > STACK_CAP) { overflow = true; cur = EMPTY_REF; return; }
             enter_instance(sc, __ldg(sc.tlas_index + first), stk, true);
         }
     }
@@ -315,7 +263,6 @@ struct TraceState {
 // Closest hit (ANY=false) or any hit (ANY=true; stops at the first accepted candidate, the commented
 // lighting_pass early-out of raycast.cu:128-132) for one ray.
 // Must be called by all 32 lanes of the warp (advance() holds a warp barrier); lanes without a ray pass active=false.
-// The kernel must have called init_pick_lut().
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ void trace(const SceneDev& sc, Stack& stk, bool active, f3 org, f3 dir, Hit& hit, Counters* ctr)
 {

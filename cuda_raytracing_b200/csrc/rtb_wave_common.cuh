@@ -28,10 +28,34 @@ XF f3 reflect_dir(f3 d, f3 n)
     return xnormalize(xsub(d, xscale(n, k)));
 }
 
+// sin and cos of phi in [0, 2 pi] without libm: the operation sequence of oracle/rt_oracle.c: sincos_2pi, in unfused binary64
+// (CUDA's sinf/cosf and glibc's differ in the last ulp on a few percent of arguments; a path-traced pixel is only reproducible
+// when both sides draw the same directions bit for bit)
+XF void sincos_2pi(float phi, float& s, float& c)
+{
+    const double x = (double)phi;
+    const int k = (int)__dadd_rn(__dmul_rn(x, 0.63661977236758134308), 0.5);
+    const double y = __dsub_rn(x, __dmul_rn((double)k, 1.57079632679489655800)), z = __dmul_rn(y, y);
+#define RTB_H(a, b) __dadd_rn(a, __dmul_rn(z, b))                     /* a + z * b */
+    const double ps = RTB_H(-1.66666666666666324348e-01, RTB_H(8.33333333332248946124e-03, RTB_H(-1.98412698298579493134e-04,
+                      RTB_H(2.75573137070700676789e-06, RTB_H(-2.50507602534068634195e-08, 1.58969099521155010221e-10)))));
+    const double pc = RTB_H(4.16666666666666019037e-02, RTB_H(-1.38888888888741095749e-03, RTB_H(2.48015872894767294178e-05,
+                      RTB_H(-2.75573143513906633035e-07, RTB_H(2.08757232129817482790e-09, -1.13596475577881948265e-11)))));
+#undef RTB_H
+    const double sp = __dadd_rn(y, __dmul_rn(__dmul_rn(y, z), ps));
+    const double cp = __dadd_rn(__dsub_rn(1.0, __dmul_rn(0.5, z)), __dmul_rn(__dmul_rn(z, z), pc));
+    const int q = k & 3;
+    const double sv = q == 0 ? sp : (q == 1 ? cp : (q == 2 ? -sp : -cp));
+    const double cv = q == 0 ? cp : (q == 1 ? -sp : (q == 2 ? -cp : sp));
+    s = __double2float_rn(sv); c = __double2float_rn(cv);
+}
+
 XF f3 cosine_dir(f3 n, float u1, float u2)
 {
     const float r = __fsqrt_rn(u1), phi = xm(6.2831853f, u2);
-    const float lx = xm(r, cosf(phi)), ly = xm(r, sinf(phi)), lz = __fsqrt_rn(fmaxf(0.0f, xs(1.0f, u1)));
+    float sphi, cphi;
+    sincos_2pi(phi, sphi, cphi);
+    const float lx = xm(r, cphi), ly = xm(r, sphi), lz = __fsqrt_rn(fmaxf(0.0f, xs(1.0f, u1)));
     const float sign = copysignf(1.0f, n.z);
     const float a = xd(-1.0f, xa(sign, n.z));
     const float b = xm(xm(n.x, n.y), a);

@@ -91,7 +91,6 @@ __global__ void __launch_bounds__(128, MINB) k_trace_queue(int refill_idle, Scen
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
     const int count = *count_ptr;
-    init_pick_lut();
     RTB_DECL_STACK(stk);
     TraceState S;
     QueueSink<ANY> sink;

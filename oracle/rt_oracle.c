@@ -791,11 +791,31 @@ static inline o_f3 reflect_dir(o_f3 d, o_f3 n)
     return o_normalize(sub3(d, scale3(n, k)));
 }
 
+/* sin and cos of phi in [0, 2 pi] WITHOUT libm, so that the CPU and the GPU produce the same bits (glibc's and CUDA's sinf/cosf
+ * differ in the last ulp on a few percent of arguments, which moved single samples of path-traced pixels): quadrant reduction
+ * and the fdlibm kernel polynomials, evaluated in binary64 with plain multiplies and adds in a fixed order (no fma), rounded to
+ * binary32 once.  The device restatement (csrc/rtb_wave_common.cuh: sincos_2pi) performs the identical operation sequence. */
+static void sincos_2pi(float phi, float* s, float* c)
+{
+    const double x = (double)phi;
+    const int k = (int)(x * 0.63661977236758134308 + 0.5);
+    const double y = x - (double)k * 1.57079632679489655800, z = y * y;
+    const double sp = y + y * z * (-1.66666666666666324348e-01 + z * (8.33333333332248946124e-03 + z * (-1.98412698298579493134e-04 +
+                      z * (2.75573137070700676789e-06 + z * (-2.50507602534068634195e-08 + z * 1.58969099521155010221e-10)))));
+    const double cp = 1.0 - 0.5 * z + z * z * (4.16666666666666019037e-02 + z * (-1.38888888888741095749e-03 + z * (2.48015872894767294178e-05 +
+                      z * (-2.75573143513906633035e-07 + z * (2.08757232129817482790e-09 + z * -1.13596475577881948265e-11)))));
+    const int q = k & 3;
+    const double sv = q == 0 ? sp : (q == 1 ? cp : (q == 2 ? -sp : -cp));
+    const double cv = q == 0 ? cp : (q == 1 ? -sp : (q == 2 ? -cp : sp));
+    *s = (float)sv; *c = (float)cv;
+}
+
 /* cosine-weighted hemisphere sample around n (Duff et al. 2017 basis) */
 static o_f3 cosine_dir(o_f3 n, float u1, float u2)
 {
-    float r = sqrtf(u1), phi = 6.2831853f * u2;
-    float lx = r * cosf(phi), ly = r * sinf(phi), lz = sqrtf(fmaxf(0.0f, 1.0f - u1));
+    float r = sqrtf(u1), phi = 6.2831853f * u2, sphi, cphi;
+    sincos_2pi(phi, &sphi, &cphi);
+    float lx = r * cphi, ly = r * sphi, lz = sqrtf(fmaxf(0.0f, 1.0f - u1));
     float sign = copysignf(1.0f, n.z);
     float a = -1.0f / (sign + n.z);
     float b = n.x * n.y * a;

@@ -393,13 +393,3 @@ def test_headless_presentation_script_overlay_png(oracle, tmp_path):
     ys, xs = np.nonzero(overlay)
     assert ys.min() >= 9 and ys.max() <= 29 and xs.min() >= 10 and xs.max() < 10 + 18 * len("FPS: 12.500000")
     assert overlay[9:30, 10:25].all(axis=1)[0]                                   # top bar of the 'F'
-
-
-def test_cwnode_quantisation_and_slab_slack(tmp_path):
-    """The compressed 8-wide node (csrc/rtb_cwnode.cuh) and the tracer's plane arithmetic (csrc/rtb_trace.cuh, restated on the
-    host operation by operation): child boxes are contained in their decoded boxes to within one cell, and for random rays the
-    computed near / far parameters bracket the exact ones -- the box test can only cull what the exact test would cull."""
-    exe = str(tmp_path / "cwnode_check")
-    subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-o", exe, os.path.join(ROOT, "tests", "cwnode_check.cpp")])
-    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and r.stdout.startswith("ok:"), r.stdout + r.stderr
