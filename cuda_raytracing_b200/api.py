@@ -59,7 +59,7 @@ class FrameStats(C.Structure):
 assert C.sizeof(CInstance) == 104 and C.sizeof(CMaterial) == 48 and C.sizeof(Lre) == 24
 
 EXPORTS = ["rtb_context_create", "rtb_context_destroy", "rtb_last_error", "rtb_version", "rtb_set_option",
-           "rtb_mesh_create", "rtb_mesh_rebuild", "rtb_mesh_info_get", "rtb_mesh_read", "rtb_mesh_destroy", "rtb_texture_upload",
+           "rtb_mesh_create", "rtb_mesh_rebuild", "rtb_mesh_rebuild_async", "rtb_mesh_commit", "rtb_mesh_info_get", "rtb_mesh_read", "rtb_mesh_destroy", "rtb_texture_upload",
            "rtb_set_materials", "rtb_set_instances", "rtb_update_instance", "rtb_render", "rtb_render_host",
            "rtb_synchronize", "rtb_frame_stats_get", "rtb_debug_math", "rtb_invert_intrinsic", "rtb_invert_lre",
            "rtb_instance_build_inv", "rtb_triangle_init", "rtb_obj_load", "rtb_free",
@@ -89,6 +89,8 @@ def lib():
     L.rtb_set_option.argtypes = [vp, C.c_char_p, ci]
     L.rtb_mesh_create.argtypes = [vp, vp, ci, ci, C.POINTER(ci)]
     L.rtb_mesh_rebuild.argtypes = [vp, ci, vp, ci, ci]
+    L.rtb_mesh_rebuild_async.argtypes = [vp, ci, vp, ci, ci]
+    L.rtb_mesh_commit.argtypes = [vp, ci]
     L.rtb_mesh_info_get.argtypes = [vp, ci, C.POINTER(MeshInfo)]
     L.rtb_mesh_destroy.argtypes = [vp, ci]
     L.rtb_mesh_read.argtypes = [vp, ci, ci, vp, C.c_size_t]
@@ -274,6 +276,13 @@ class Scene:
         else:
             t = np.ascontiguousarray(triangles, TRI)
             _check(lib().rtb_mesh_rebuild(self._ctx, self.mesh_ids[index], t.ctypes.data, len(t), 0))
+
+    def rebuild_mesh_async(self, index, device_ptr, n):
+        """Enqueue the rebuild on the library's build stream (next to the frame being rendered); commit_mesh() swaps it in."""
+        _check(lib().rtb_mesh_rebuild_async(self._ctx, self.mesh_ids[index], device_ptr, n, 1))
+
+    def commit_mesh(self, index):
+        _check(lib().rtb_mesh_commit(self._ctx, self.mesh_ids[index]))
 
     def mesh_info(self, index):
         info = MeshInfo()

@@ -23,12 +23,23 @@ static int cuda_fail(cudaError_t e, const char* where)
 
 namespace rtb { void wave_release(void* state); }
 
+struct BlasBack {                   // the buffer an asynchronous rebuild writes while frames still read the front one
+    float4* tri_rec = nullptr; float2* uvs = nullptr;
+    int tri_cap = 0, n = 0;
+    BvhResult bvh;
+    cudaEvent_t built = nullptr;    // recorded after the build's last kernel and its counter read-back
+    void* counters_h = nullptr;     // pinned
+    bool pending = false;           // a build has been enqueued and not committed yet
+    float build_ms = 0.f;
+};
+
 struct MeshRec {
     bool alive = false;
     int n = 0;
     float4* tri_rec = nullptr; float2* uvs = nullptr;
     int tri_cap = 0;
     BvhResult bvh;
+    BlasBack back;                  // allocated by the first rtb_mesh_rebuild_async
     rtb_mesh_info info{};
     // what the TLAS knows about this mesh (see mesh_cut / pack_instance)
     bool dynamic = false;           // rebuilt at least once: its world boxes come from the (slightly inflated) root bounds
@@ -62,6 +73,9 @@ struct rtb_context {
     int32_t* aov_prim_d = nullptr; int32_t* aov_inst_d = nullptr; float* aov_t_d = nullptr; size_t aov_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t frame_done = nullptr;   // recorded after every rtb_render on its stream: BLAS / TLAS / material updates (stream 0) wait for it
+    cudaStream_t build_stream = nullptr;    // asynchronous rebuilds (rtb_mesh_rebuild_async) run here, next to the frame being rendered
+    Arena ws_async, stage_async;        // their workspace (the synchronous path keeps its own: the two may overlap in time)
+    cudaEvent_t ev_b0 = nullptr;
     float last_ms = 0.f;
     int last_launches = 0;
     int opt_counters = 0, opt_leaf = 8, opt_key_bits = 0;
@@ -102,6 +116,12 @@ int rtb_context_create(int device, rtb_context** out)
 
 static void free_mesh(MeshRec& m)
 {
+    if (m.back.tri_rec) cudaFree(m.back.tri_rec);
+    if (m.back.uvs) cudaFree(m.back.uvs);
+    if (m.back.bvh.nodes) cudaFree(m.back.bvh.nodes);
+    if (m.back.bvh.order) cudaFree(m.back.bvh.order);
+    if (m.back.built) cudaEventDestroy(m.back.built);
+    if (m.back.counters_h) cudaFreeHost(m.back.counters_h);
     if (m.tri_rec) cudaFree(m.tri_rec);
     if (m.uvs) cudaFree(m.uvs);
     if (m.bvh.nodes) cudaFree(m.bvh.nodes);
@@ -130,7 +150,9 @@ void rtb_context_destroy(rtb_context* c)
     if (c->aov_inst_d) cudaFree(c->aov_inst_d);
     if (c->aov_t_d) cudaFree(c->aov_t_d);
     wave_release(c->wf);
-    c->ws.release(); c->stage.release();
+    c->ws.release(); c->stage.release(); c->ws_async.release(); c->stage_async.release();
+    if (c->build_stream) cudaStreamDestroy(c->build_stream);
+    if (c->ev_b0) cudaEventDestroy(c->ev_b0);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->frame_done) cudaEventDestroy(c->frame_done);
@@ -202,6 +224,8 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
     return RTB_OK;
 }
 
+static void after_rebuild(rtb_context* c, MeshRec& m, int id, bool had_dynamic_box, int n);
+
 int rtb_mesh_create(rtb_context* c, const rtb_triangle* tris, int n, int on_device, int* mesh_id)
 {
     if (!c || n < 0 || (n > 0 && !tris) || !mesh_id) return fail(RTB_ERR_INVALID, "rtb_mesh_create: bad argument");
@@ -221,14 +245,88 @@ int rtb_mesh_rebuild(rtb_context* c, int id, const rtb_triangle* tris, int n, in
     m.cut_valid = false;
     int rc = build_mesh(c, m, tris, n, on_device);
     if (rc != RTB_OK) return rc;
+    after_rebuild(c, m, id, had_dynamic_box, n);
+    return RTB_OK;
+}
+
+// The instance world boxes in the TLAS were made from the OLD geometry.  A deforming mesh keeps them as long as its new bounds
+// stay inside the (inflated) box they were made from -- no TLAS work in the steady state of an animation -- otherwise the TLAS
+// is rebuilt before the next frame (make_scene).
+static void after_rebuild(rtb_context* c, MeshRec& m, int id, bool had_dynamic_box, int n)
+{
     m.dynamic = true;
-    // The instance world boxes in the TLAS were made from the OLD geometry.  A deforming mesh keeps them as long as its new
-    // bounds stay inside the (inflated) box they were made from -- no TLAS work in the steady state of an animation --
-    // otherwise the TLAS is rebuilt before the next frame (make_scene).
     bool covered = had_dynamic_box && n > 0;
     for (int k = 0; k < 3 && covered; k++) covered = m.bvh.bounds[k] >= m.cut[k] && m.bvh.bounds[k + 3] <= m.cut[k + 3];
     if (covered) m.cut_valid = true;
     else for (const auto& in : c->instances_h) if (in.mesh_index == id) { c->tlas_dirty = true; break; }
+}
+
+int rtb_mesh_rebuild_async(rtb_context* c, int id, const rtb_triangle* tris, int n, int on_device)
+{
+    if (!c || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive || n < 0 || (n > 0 && !tris))
+        return fail(RTB_ERR_INVALID, "rtb_mesh_rebuild_async: bad argument");
+    if (!on_device) return fail(RTB_ERR_INVALID, "rtb_mesh_rebuild_async: the triangles must be resident on the device (a pageable host copy would synchronise)");
+    MeshRec& m = c->meshes[id];
+    BlasBack& b = m.back;
+    if (b.pending) return fail(RTB_ERR_STATE, "rtb_mesh_rebuild_async: the previous asynchronous rebuild of this mesh was not committed");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    if (!c->build_stream) {
+        CU(cudaStreamCreateWithFlags(&c->build_stream, cudaStreamNonBlocking), "build stream");
+        CU(cudaEventCreate(&c->ev_b0), "cudaEventCreate");
+    }
+    if (!b.built) {
+        CU(cudaEventCreate(&b.built), "cudaEventCreate");
+        CU(cudaMallocHost(&b.counters_h, build_counters_bytes()), "cudaMallocHost");
+    }
+    cudaStream_t st = c->build_stream;
+    const size_t nn = (size_t)(n > 0 ? n : 1);
+    if (b.tri_cap < n || !b.tri_rec) {
+        if (b.tri_rec) cudaFree(b.tri_rec);
+        if (b.uvs) cudaFree(b.uvs);
+        b.tri_rec = nullptr; b.uvs = nullptr;
+        CU(cudaMalloc((void**)&b.tri_rec, sizeof(float4) * TRI_F4 * nn), "cudaMalloc triangle records");
+        CU(cudaMalloc((void**)&b.uvs, sizeof(float2) * 3 * nn), "cudaMalloc uvs");
+        b.tri_cap = (int)nn;
+    }
+    // (this buffer was the front buffer until the last commit: that commit made the build stream wait for its last reader)
+    c->stage_async.reset();
+    CU(c->stage_async.reserve(nn * 32 + 4096), "stage reserve");
+    float4* bmin = c->stage_async.take<float4>(nn);
+    float4* bmax = c->stage_async.take<float4>(nn);
+    CU(cudaEventRecord(c->ev_b0, st), "event");
+    const int key_bits = c->opt_key_bits ? c->opt_key_bits : (n > (1 << 21) ? 64 : 32);
+    CU(build_bvh(tris, bmin, bmax, n, c->opt_leaf, key_bits, c->sah_node_cost, b.bvh, c->ws_async, st, b.tri_rec, b.uvs, b.built, b.counters_h), "build_bvh");
+    b.n = n; b.pending = true;
+    return RTB_OK;
+}
+
+int rtb_mesh_commit(rtb_context* c, int id)
+{
+    if (!c || id < 0 || id >= (int)c->meshes.size() || !c->meshes[id].alive) return fail(RTB_ERR_INVALID, "rtb_mesh_commit: bad argument");
+    MeshRec& m = c->meshes[id];
+    BlasBack& b = m.back;
+    if (!b.pending) return fail(RTB_ERR_STATE, "rtb_mesh_commit: no asynchronous rebuild pending for this mesh");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    CU(cudaEventSynchronize(b.built), "build sync");          // the HOST waits for the build only; frames in flight keep running
+    b.pending = false;
+    CU(build_bvh_finish(b.bvh, b.counters_h), "build_bvh (asynchronous)");
+    cudaEventElapsedTime(&b.build_ms, c->ev_b0, b.built);
+    // The frames enqueued so far traverse the old front buffer, which becomes the target of the NEXT asynchronous build: the
+    // build stream waits here for the last of them (frame_done as recorded by that frame); later frames read the new buffer.
+    CU(cudaStreamWaitEvent(c->build_stream, c->frame_done, 0), "order the next build after the frames in flight");
+    const bool had_dynamic_box = m.dynamic && m.cut_valid && m.cut.size() == 6;
+    m.cut_valid = false;
+    std::swap(m.tri_rec, b.tri_rec); std::swap(m.uvs, b.uvs); std::swap(m.tri_cap, b.tri_cap); std::swap(m.n, b.n);
+    std::swap(m.bvh, b.bvh);
+    const size_t nn = (size_t)(m.n > 0 ? m.n : 1);
+    rtb_mesh_info& I = m.info;
+    I.num_triangles = m.n; I.num_nodes = m.bvh.num_nodes; I.num_leaves = m.bvh.num_leaves; I.max_leaf_size = m.bvh.max_leaf;
+    I.depth = m.bvh.depth; I.stack_need = 3 * m.bvh.depth + 2; I.build_ms = b.build_ms; I.sah_cost = m.bvh.sah;
+    for (int k = 0; k < 3; k++) { I.bounds_min[k] = m.bvh.bounds[k]; I.bounds_max[k] = m.bvh.bounds[k + 3]; }
+    I.device_bytes = sizeof(float4) * TRI_F4 * nn + sizeof(float2) * 3 * nn + sizeof(float4) * NODE_F4 * (size_t)m.bvh.node_cap +
+                     sizeof(unsigned) * (size_t)m.bvh.order_cap;
+    c->mesh_table_dirty = true;
+    after_rebuild(c, m, id, had_dynamic_box, m.n);
     return RTB_OK;
 }
 

@@ -526,8 +526,27 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     return cudaGetLastError();
 }
 
+static cudaError_t read_counters(BvhResult& out, const BuildCounters& h, int n)
+{
+    auto dec = [](int i) { int j = i >= 0 ? i : i ^ 0x7fffffff; float f; memcpy(&f, &j, 4); return f; };
+    for (int k = 0; k < 6; k++) out.bounds[k] = dec(h.bounds[k]);
+    if (n <= 1) { out.num_nodes = 1; out.num_leaves = n; out.max_leaf = n; out.depth = 1; out.sah = 0.f; }
+    else {
+        out.num_nodes = h.n_wide; out.num_leaves = h.n_leaves; out.max_leaf = h.max_leaf; out.depth = h.max_level + 1; out.sah = h.sah;
+        if (h.qcount[70] != 0) return cudaErrorLaunchFailure;      // tree deeper than the level loop: refuse, never truncate
+    }
+    return cudaSuccess;
+}
+
+size_t build_counters_bytes() { return sizeof(BuildCounters); }
+
+cudaError_t build_bvh_finish(BvhResult& out, const void* host_counters)
+{
+    return read_counters(out, *(const BuildCounters*)host_counters, out.n);
+}
+
 cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, float sah_node_cost, BvhResult& out,
-                      Arena& ws, cudaStream_t st, float4* tri_rec, float2* uvs, cudaEvent_t done)
+                      Arena& ws, cudaStream_t st, float4* tri_rec, float2* uvs, cudaEvent_t done, void* deferred_counters)
 {
     // outputs (grow-only)
     int need_nodes = n > 1 ? n : 1;
@@ -571,17 +590,18 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
         if (((uintptr_t)tris_dev & 7u) == 0) k_emit_tris<true><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, out.order, tri_rec, uvs);
         else k_emit_tris<false><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, out.order, tri_rec, uvs);
     }
+    if (deferred_counters) {
+        // asynchronous build: the counters travel to pinned host memory on the stream, `done` is recorded after them and the
+        // caller reads them with build_bvh_finish() once that event has completed -- no host synchronisation here
+        CK(cudaMemcpyAsync(deferred_counters, ctr, sizeof(BuildCounters), cudaMemcpyDeviceToHost, st));
+        if (done) CK(cudaEventRecord(done, st));
+        return cudaSuccess;
+    }
     if (done) CK(cudaEventRecord(done, st));
     BuildCounters h;
     CK(cudaMemcpyAsync(&h, ctr, sizeof h, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    auto dec = [](int i) { int j = i >= 0 ? i : i ^ 0x7fffffff; float f; memcpy(&f, &j, 4); return f; };
-    for (int k = 0; k < 6; k++) out.bounds[k] = dec(h.bounds[k]);
-    if (n <= 1) { out.num_nodes = 1; out.num_leaves = n; out.max_leaf = n; out.depth = 1; out.sah = 0.f; }
-    else {
-        out.num_nodes = h.n_wide; out.num_leaves = h.n_leaves; out.max_leaf = h.max_leaf; out.depth = h.max_level + 1; out.sah = h.sah;
-        if (h.qcount[70] != 0) return cudaErrorLaunchFailure;      // tree deeper than the level loop: refuse, never truncate
-    }
+    CK(read_counters(out, h, n));
     return cudaSuccess;
 }
 

@@ -36,7 +36,13 @@ struct BvhResult {
 // counters at the end.
 // sah_node_cost: cost of one wide-node child box relative to one triangle test in the SAH leaf decision (option "sah_node").
 cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, float sah_node_cost, BvhResult& out,
-                      Arena& ws, cudaStream_t st, float4* tri_rec = nullptr, float2* uvs = nullptr, cudaEvent_t done = nullptr);
+                      Arena& ws, cudaStream_t st, float4* tri_rec = nullptr, float2* uvs = nullptr, cudaEvent_t done = nullptr,
+                      void* deferred_counters = nullptr);
+// Asynchronous form: with `deferred_counters` (pinned host memory of build_counters_bytes()) build_bvh does not synchronise; the
+// counters are copied there on the stream BEFORE `done` is recorded, and build_bvh_finish() turns them into out.num_nodes,
+// depth, bounds ... once the caller has seen `done` complete.
+size_t build_counters_bytes();
+cudaError_t build_bvh_finish(BvhResult& out, const void* host_counters);
 
 
 }  // namespace rtb

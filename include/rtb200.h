@@ -110,6 +110,13 @@ RTB_API int rtb_mesh_create(rtb_context* ctx, const rtb_triangle* tris, int n, i
  * frame.  Like every scene-changing call it runs on the default stream and returns when the device has finished; a frame
  * still in flight on a NON-blocking stream must be waited for first (the reference has one stream and the same rule). */
 RTB_API int rtb_mesh_rebuild(rtb_context* ctx, int mesh_id, const rtb_triangle* tris, int n, int tris_on_device);
+/* The same rebuild off the frame's critical path (config C5: build frame f+1 while frame f renders).  _async enqueues the whole
+ * build on the context's own build stream into the mesh's BACK buffer (the triangles must be on the device and stay untouched
+ * until the commit) and returns at once; frames keep traversing the front buffer.  _commit waits -- the host, for that build
+ * only -- swaps the buffers and refreshes rtb_mesh_info; frames enqueued afterwards see the new BLAS.  One build per mesh may be
+ * pending.  No counterpart in the reference (its BVH is built once on the host, BVHTree.hpp:203-292). */
+RTB_API int rtb_mesh_rebuild_async(rtb_context* ctx, int mesh_id, const rtb_triangle* tris_on_device, int n, int tris_on_device_flag);
+RTB_API int rtb_mesh_commit(rtb_context* ctx, int mesh_id);
 RTB_API int rtb_mesh_info_get(rtb_context* ctx, int mesh_id, rtb_mesh_info* out);
 RTB_API int rtb_mesh_destroy(rtb_context* ctx, int mesh_id);
 /* Inspection (tools/tests; the analogue of BVHTree::print_stats, BVHTree.hpp:117-172): copies device arrays to the host.

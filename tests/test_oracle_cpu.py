@@ -245,6 +245,7 @@ def test_cabi_rejects_null_arguments_without_a_device(rtb):
     L = rtb.lib()
     calls = {
         "rtb_set_option": (None, b"counters", 1), "rtb_mesh_create": (None, None, 0, 0, None), "rtb_mesh_rebuild": (None, 0, None, 0, 0),
+        "rtb_mesh_rebuild_async": (None, 0, None, 0, 1), "rtb_mesh_commit": (None, 0),
         "rtb_mesh_info_get": (None, 0, None), "rtb_mesh_destroy": (None, 0), "rtb_mesh_read": (None, 0, 0, None, 0),
         "rtb_texture_upload": (None, None, 0, 0, None, None), "rtb_set_materials": (None, None, 0), "rtb_set_instances": (None, None, 0),
         "rtb_update_instance": (None, 0, None), "rtb_render": (None, None, None, 0, None, None), "rtb_render_host": (None, None, None, 0, None),

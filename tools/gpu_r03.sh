@@ -9,7 +9,7 @@ timeout 400 python bench.py --config c4 --no-cpu-baseline --no-ref-cuda --steps 
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-ref-cuda"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_c3.csv $CMD > $O/ncu_launch.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_megaq -s 3 -c 1 -o $O/prof_megaq_c3 $CMD > $O/ncu_megaq.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"k_mega<" -s 3 -c 1 -o $O/prof_mega_share8 python tools/tune.py c3 tile_count=8 fused=1 > $O/ncu_mega8.log 2>&1
+ncu --set full --clock-control none --import-source on -k k_mega -s 3 -c 1 -o $O/prof_mega_share8 python tools/tune.py c3 tile_count=8 fused=1 > $O/ncu_mega8.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_megaq -s 2 -c 1 -o $O/prof_megaq_c4 python tools/tune.py c4 fused=2 > $O/ncu_megaq_c4.log 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/build_launches.csv python tools/build_prof.py 1582 3161 2 > $O/ncu_build.log 2>&1
 python tools/tune.py c3 tile_count=8 fused=1,2 cost_block=3,2,1,0 > $O/tune_share8.log 2>&1; cat $O/tune_share8.log
