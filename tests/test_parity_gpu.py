@@ -687,7 +687,7 @@ def test_c5_full_size_frame(rtb, oracle):
 
 
 def test_c5_full_size_build_invariants(rtb):
-    """C5's 10M-triangle mesh (48-bit Morton keys): the leaf order is a permutation, the leaves tile it exactly once, every
+    """C5's 10M-triangle mesh (39-bit Morton keys, five radix passes): the leaf order is a permutation, the leaves tile it exactly once, every
     interior node is referenced once, the root's child boxes span the mesh; a rebuild gives the same tree up to node numbering."""
     import bench
     cfg = bench.CONFIGS["c5"]

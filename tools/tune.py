@@ -40,7 +40,7 @@ def main():
                 scene.set_option(k, v)
         ms = []
         for i in range(7):
-            cam.pose = np.array(bench.camera_pose(cfg, i), np.float32)
+            cam.pose = np.array(bench.camera_pose(cfg, 3 if os.environ.get("SAMEPOSE") else i), np.float32)
             if not os.environ.get("NOFLUSH"): flush.fill_(i)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
