@@ -233,6 +233,7 @@ def main():
     ap.add_argument("--config", default="c3")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--ref-cuda-as-shipped", action="store_true", help="also time the reference kernel exactly as shipped (UB Q_rsqrt), +25 s")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--exchange", default="direct", choices=["direct", "push", "nccl"],
                     help="N>1: how the bands reach rank 0 (tiles.PeerFrame direct stores / peer copy, or the NCCL gather)")
@@ -456,6 +457,8 @@ def main():
                 import refcuda
                 poses = [camera_pose(cfg, args.warmup + k) for k in range(min(args.steps, 4))]
                 ref_cuda = refcuda.time_reference_kernel(tris, scene_materials(cfg), scene_instances(cfg), W, H, K, D, poses)
+                if args.ref_cuda_as_shipped and os.path.exists(refcuda.PATH_ASIS):
+                    ref_cuda["as_shipped"] = refcuda.time_reference_kernel(tris, scene_materials(cfg), scene_instances(cfg), W, H, K, D, poses, as_shipped=True)
             except Exception as ex:                      # the reported baseline is optional, the bench line is not
                 ref_cuda = dict(error=str(ex)[:200])
 

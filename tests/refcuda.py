@@ -45,13 +45,13 @@ class RefCuda(orc.RefHost):
         return out
 
 
-def time_reference_kernel(tris, materials, instances, W, H, K, D, poses):
+def time_reference_kernel(tris, materials, instances, W, H, K, D, poses, as_shipped=False):
     """Reference CUDA kernel (P2 variant) on the same scene and the same camera poses as the bench's timed loop: ms/frame and
     Mrays/s (primary rays only -- the reference traces nothing else).  One untimed frame first (module load), then every pose is
     timed once by the harness's own CUDA events, L2 flushed before it like in the timed loop."""
     import time
     import torch
-    R = RefCuda()
+    R = RefCuda(PATH_ASIS if as_shipped else PATH)  # as shipped: Q_rsqrt reads a `long` (8 bytes on LP64) -- undefined behaviour, kept for the record
     t0 = time.perf_counter()
     mesh = R.mesh_create(tris)                      # the reference's host BVHTree build (single-threaded)
     t_build = time.perf_counter() - t0
@@ -70,6 +70,6 @@ def time_reference_kernel(tris, materials, instances, W, H, K, D, poses):
             raise RuntimeError("reference kernel failed")
         ms.append(out["ms"])
     m = float(np.mean(ms))
-    return dict(kind="reference CUDA kernel (raycast.cu, sm_100a, 32-bit Q_rsqrt), primary rays only", ms_per_frame=m,
+    return dict(kind="reference CUDA kernel (raycast.cu, sm_100a, %s), primary rays only" % ("exactly as shipped" if as_shipped else "32-bit Q_rsqrt"), ms_per_frame=m,
                 value=W * H / (m * 1e-3) / 1e6, unit="Mrays/s", host_bvh_build_s=t_build, upload_s=t_upload, frames=len(ms),
                 poses="the first %d timed poses of the bench loop, L2 flushed before each" % len(ms))

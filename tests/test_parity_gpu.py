@@ -228,6 +228,28 @@ def test_instances_textures_shadow(rtb, oracle, mode):
     compare(got, ref, "instanced mode %d" % mode, explain=dict(osc=osc, W=320, H=240, K=K, D=synth.REF_D, pose=pose, mode=mode))
 
 
+@pytest.mark.parametrize("offset", [1.0e4, -3.0e5])
+def test_scene_far_from_the_origin(rtb, oracle, offset):
+    """The instanced scene translated far from the origin (|coordinates| ~ 1e4 .. 3e5, one binary32 ulp there is 1e-3 .. 3e-2):
+    the reference's inverse-pose round trip then errs by many ulps of the coordinates, not of the distance; the pruning bound
+    (TraceState::begin: tslack) must scale with the coordinate magnitude or a candidate the reference would prefer gets culled."""
+    meshes, mats, insts = instanced_case(3)
+    shift = np.array([offset, -0.7 * offset, 0.3 * offset], np.float64)
+    insts = [(m, a, tuple((np.array(p[:3], np.float64) + shift).astype(np.float32).tolist()) + tuple(p[3:]), sc) for (m, a, p, sc) in insts]
+    K = synth.C1_K * HALF_K
+    pose = tuple((np.array([0.5, -6.0, 2.5], np.float64) + shift).astype(np.float32).tolist()) + (0.05, -0.3, 0.02)
+    s = make_rtb_scene(rtb, meshes, mats, insts)
+    got = render_rtb(rtb, s, 320, 240, K, synth.REF_D, pose, mode=1)
+    s.close()
+    osc = make_oracle_scene(oracle, meshes, mats, insts)
+    ref = osc.render(320, 240, K, synth.REF_D, pose, mode=1)
+    assert (ref["prim"] >= 0).mean() > 0.2
+    # at these magnitudes the reference itself is noisy (its hit points jump by ulps of 1e4): ids may differ where its own
+    # round trip reorders near-equal distances -- every such pixel must still be explained; t stays within 1e-5 of ITS value
+    compare(got, ref, "scene translated by %g" % offset, id_budget=2e-3, colour_budget=2e-3,
+            explain=dict(osc=osc, W=320, H=240, K=K, D=synth.REF_D, pose=pose, mode=1))
+
+
 @pytest.mark.parametrize("fused", [2, 1, 0])
 def test_reflections_wavefront(rtb, oracle, fused):
     """mode 2 through the fused persistent kernel (default) and through the staged wavefront pipeline."""
