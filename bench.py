@@ -368,7 +368,7 @@ def main():
     cpu = None
     ref_cuda = None
     own_target = target if not (world > 1 and args.exchange == "nccl") else frame.data_ptr()
-    kt, variants = [], set()
+    kt, xt, variants = [], [], set()
     for k in range(args.steps):
         cam.pose = np.array(camera_pose(cfg, args.warmup + k), np.float32)
         if not args.no_flush:
@@ -377,8 +377,17 @@ def main():
         e0.record(stream)
         cam.render_scene(scene, own_target, pitch, stream=C.c_void_p(stream.cuda_stream))
         e1.record(stream)
+        if world > 1:                                    # the exchange / completion signal alone, after this rank's own launch
+            e2 = torch.cuda.Event(enable_timing=True)
+            if isinstance(fg, tiles.PeerFrame):
+                fg.gather(stream.cuda_stream)
+            else:
+                fg.gather(frame)
+            e2.record(stream)
         torch.cuda.synchronize()
         kt.append(e0.elapsed_time(e1))
+        if world > 1:
+            xt.append(e1.elapsed_time(e2))
         variants.add(scene.frame_stats()["kernel_variant"])
     kms = float(np.mean(kt))
     n_count = min(args.steps, 2 if cfg["mode"] == 3 else args.steps)       # path tracing: the counting variant costs seconds per frame
@@ -421,6 +430,7 @@ def main():
         traffic = prof.get("dram_bytes") if world == 1 else None             # the capture is of the full frame on one GPU
         roof = dict(bound=prof.get("bound", "issue"), achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=traffic, peak_kind=peak_kind,
                     kernel=kname, kernel_variant=variant, kernel_ms=kms, kernel_ms_ranks=dict(min=float(kall.min()), median=float(np.median(kall)), max=float(kall.max())),
+                    exchange_ms=(float(np.mean(xt)) if xt else 0.0),     # rank 0: its wait for the other ranks' bands after its own launch (includes their skew)
                     share_of_step=kms / (ms / args.steps), frames="the %d timed poses, L2 flushed, this rank's share (1/%d of the bands)" % (args.steps, world),
                     ceilings=dict(hbm=dict(achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, alg_bytes=alg_bytes,
                                            dram_frac=(traffic / (kms * 1e-3) / 1e9 / peak) if traffic else None),

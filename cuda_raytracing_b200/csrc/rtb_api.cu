@@ -170,6 +170,7 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     else if (n == "inst_cut") { c->opt_inst_cut = std::max(1, std::min(value, 1024)); c->tlas_dirty = !c->instances_h.empty(); }
     else if (n == "fused") c->tune.fused = value;
     else if (n == "cost_order") c->tune.cost_order = value;
+    else if (n == "ring_split") c->tune.ring_split = value ? 1 : 0;
     else if (n == "cost_block") c->tune.cost_block = std::max(0, std::min(value, 3));
     else if (n == "queue_keep") c->tune.queue_keep = std::max(1, std::min(value, 33));
     else if (n == "tail_idle") c->tune.tail_idle = std::max(1, std::min(value, 32));

@@ -371,7 +371,7 @@ XF int ring_try_claim(const QRing& Q, int r, bool any, unsigned& h)
 }
 
 template <bool PATH, bool COUNT, int MINB>
-__global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, FrameParams P, MegaGeo G, int* __restrict__ head, QRing Q, MegaBufs B,
+__global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, int ring_split, SceneDev sc, FrameParams P, MegaGeo G, int* __restrict__ head, QRing Q, MegaBufs B,
                                                      unsigned char* __restrict__ img, size_t pitch, int32_t* __restrict__ aov_prim,
                                                      int32_t* __restrict__ aov_inst, float* __restrict__ aov_t, Counters* ctr)
 {
@@ -408,22 +408,33 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, SceneDev sc, 
         }
         const unsigned nm = __ballot_sync(0xffffffffu, next);
         bool kept = false;                                      // warp-uniform: the rays stayed in their lanes (ring full)
-        if (nm) {                                               // append the continuing rays: one atomic per warp
+        if (nm) {                                               // append the continuing rays: one atomic per warp and ray kind
+            // Rays of a kind go to the same ring (ring_split): shadow rays (short: any-hit, most leave their own instance and
+            // meet nothing) to the odd ring of the CTA's pair, closest-hit continuation rays to the even one, so that the 32 rays
+            // a warp later starts together are of similar length -- a warp runs until its slowest ray is done.
+            const unsigned sm = ring_split ? __ballot_sync(0xffffffffu, next && (nmeta & 1u)) : 0u;   // shadow rays
+            const unsigned cm = nm & ~sm;
+            const int rs = ring_split ? (r0 | 1) : r0, rc = ring_split ? (r0 & ~1) : r0;
             const int leader = __ffs(nm) - 1;
-            unsigned base = 0xffffffffu;
+            unsigned base_c = 0xffffffffu, base_s = 0xffffffffu;
             // a generation that stays wide enough keeps its lanes; so does every generation once the tiles are gone (the
             // frame tail is latency-bound: a queue hop only delays the chain)
             if (lane == leader && __popc(nm) < keep_thr && *(volatile int*)head < G.n_slots) {
-                unsigned* c = Q.ctl + (size_t)r0 * QR_CTL;
-                const unsigned used = ld_volatile_u32(c + 32) - ld_volatile_u32(c);
-                if (used + QR_MARGIN <= Q.cap) base = atomicAdd(c + 32, (unsigned)__popc(nm));
+                unsigned* cc = Q.ctl + (size_t)rc * QR_CTL;
+                unsigned* cs = Q.ctl + (size_t)rs * QR_CTL;
+                const unsigned used_c = ld_volatile_u32(cc + 32) - ld_volatile_u32(cc), used_s = ld_volatile_u32(cs + 32) - ld_volatile_u32(cs);
+                if (used_c + QR_MARGIN <= Q.cap && used_s + QR_MARGIN <= Q.cap) {
+                    base_c = cm ? atomicAdd(cc + 32, (unsigned)__popc(cm)) : 0u;
+                    base_s = sm ? atomicAdd(cs + 32, (unsigned)__popc(sm)) : 0u;
+                }
             }
-            base = __shfl_sync(0xffffffffu, base, leader);
-            kept = base == 0xffffffffu;
+            base_c = __shfl_sync(0xffffffffu, base_c, leader); base_s = __shfl_sync(0xffffffffu, base_s, leader);
+            kept = base_c == 0xffffffffu;
             if (next) {
                 if (!kept) {
-                    const unsigned pos = base + __popc(nm & lt), slot = pos & (Q.cap - 1u);
-                    const size_t e = (size_t)r0 * Q.cap + slot;
+                    const bool sh = (sm >> lane) & 1u;
+                    const unsigned pos = sh ? base_s + __popc(sm & lt) : base_c + __popc(cm & lt), slot = pos & (Q.cap - 1u);
+                    const size_t e = (size_t)(sh ? rs : rc) * Q.cap + slot;
                     st_stream(Q.org + e, make_float4(no.x, no.y, no.z, __int_as_float(idx)));
                     st_stream(Q.dir + e, make_float4(nd.x, nd.y, nd.z, __uint_as_float(nmeta)));
                     __threadfence();
@@ -627,7 +638,7 @@ cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const 
         Q.cap = (unsigned)m->q_cap;
         MegaGeo GQ = G;
         GQ.order = nullptr;                                             // no cost map in this variant
-#define RTB_MEGAQ(PATH, COUNT, MINB) k_megaq<PATH, COUNT, MINB><<<grid, 128, 0, st>>>(tune.queue_keep, sc, P, GQ, m->head, Q, m->b, img, pitch, aov.prim, aov.inst, aov.t, ctr)
+#define RTB_MEGAQ(PATH, COUNT, MINB) k_megaq<PATH, COUNT, MINB><<<grid, 128, 0, st>>>(tune.queue_keep, (PATH) ? 0 : tune.ring_split, sc, P, GQ, m->head, Q, m->b, img, pitch, aov.prim, aov.inst, aov.t, ctr)
 #define RTB_MEGAQ_MB(PATH) do { if (count) RTB_MEGAQ(PATH, true, 4); else if (mb <= 5) RTB_MEGAQ(PATH, false, 5); \
                                 else if (mb == 6) RTB_MEGAQ(PATH, false, 6); else RTB_MEGAQ(PATH, false, 8); } while (0)
         if (path) RTB_MEGAQ_MB(true); else RTB_MEGAQ_MB(false);

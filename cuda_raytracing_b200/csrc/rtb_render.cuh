@@ -12,6 +12,7 @@ struct Tune {
                             // 0 = staged wavefront pipeline, -1 = choose 1 or 2 per frame (launch_mega: queues pay off from ~3 M pixel slots)
     int smem_top = 0;       // BLAS nodes (top levels, BFS prefix) staged in shared memory by TMA bulk copy; 0 = off (measured slower: profiles/r01e_tune_c3_smem_top.log)
     int queue_keep = 28;    // queue variant (fused=2): a warp whose continuing rays number at least this keeps them in their lanes
+    int ring_split = 1;     // queue variant: shadow rays and continuation rays go to separate rings (warps start 32 rays of one kind)
     int tail_idle = 2;      // fused kernel, after the last pixel was claimed: retire once this many live lanes are idle
     int cost_order = 1;     // fused kernel: claim pixel blocks by descending cost of the previous frame (rtb_mega.cu)
     int cost_block = 3;     // ... a block being 2^cost_block x 2^cost_block warp tiles of 8 x 4 pixels
