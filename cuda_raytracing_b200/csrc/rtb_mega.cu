@@ -103,22 +103,44 @@ XF bool slot_to_pixel(const FrameParams& P, const MegaGeo& G, int idx, int& x, i
     return tx < G.tiles_x && ty < G.tile_rows && x < P.width && y < P.height;
 }
 
-// order[] = blocks sorted by descending log-bucketed cost (counting sort, one CTA), cost[] cleared for the new frame
-__global__ void __launch_bounds__(1024) k_order(unsigned* __restrict__ cost, int nb, int* __restrict__ order)
+// order[] = blocks sorted by descending log-bucketed cost (counting sort, one CTA), cost[] cleared for the new frame.
+// rows != 0: the key of a block is the cost of its whole ROW of blocks (nbx blocks per row).  An orbiting camera shifts the image
+// sideways by more than a block per frame, so last frame's cost of a block says little about this frame's; the cost profile over
+// the image rows (sky above, geometry below) survives the shift, and what the order has to achieve is only that the LAST pixels
+// claimed are cheap ones: the launch ends one longest-remaining-chain after the last claim.
+__global__ void __launch_bounds__(1024) k_order(unsigned* __restrict__ cost, int nb, int nbx, int rows, int* __restrict__ order)
 {
     __shared__ unsigned hist[256];
     __shared__ unsigned offs[256];
+    __shared__ unsigned rowc[1024];
+    const int nby = (nb + nbx - 1) / nbx;
+    const bool by_row = rows == 1 && nby <= 1024;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) rowc[i] = 0;
     __syncthreads();
+    if (by_row) {
+        for (int b = threadIdx.x; b < nb; b += blockDim.x) atomicAdd(&rowc[b / nbx], cost[b]);
+        __syncthreads();
+    }
+    auto block_cost = [&](int b) -> unsigned {
+        if (by_row) return rowc[b / nbx];
+        if (rows == 0 || rows == 2) return cost[b];
+        unsigned c = 0;                                     // rows == 3: the largest cost within +-2 blocks of the same row
+        const int x = b % nbx, r0 = b - x;
+        for (int d = -2; d <= 2; d++) if (x + d >= 0 && x + d < nbx && r0 + x + d < nb) c = max(c, cost[r0 + x + d]);
+        return c;
+    };
     for (int b = threadIdx.x; b < nb; b += blockDim.x) {
-        const int key = 255 - min(255, (int)(log2f((float)cost[b] + 1.0f) * 8.0f));
+        const unsigned c = block_cost(b);
+        const int key = 255 - min(255, (int)(log2f((float)c + 1.0f) * 8.0f));
         atomicAdd(&hist[key], 1u);
     }
     __syncthreads();
     if (threadIdx.x == 0) { unsigned run = 0; for (int i = 0; i < 256; i++) { offs[i] = run; run += hist[i]; } }
     __syncthreads();
     for (int b = threadIdx.x; b < nb; b += blockDim.x) {
-        const int key = 255 - min(255, (int)(log2f((float)cost[b] + 1.0f) * 8.0f));
+        const unsigned c = block_cost(b);
+        const int key = 255 - min(255, (int)(log2f((float)c + 1.0f) * 8.0f));
         order[atomicAdd(&offs[key], 1u)] = b;
     }
     __syncthreads();
@@ -399,6 +421,7 @@ __global__ void __launch_bounds__(128, MINB) k_megaq(int keep_thr, int ring_spli
         if (idx >= 0) {
             const Retired R = retire_ray<PATH>(sc, P, G, B, idx, meta, sink.hmin, S.dir, L, aov_prim, aov_inst, aov_t);
             next = R.next; ended = R.ended; no = R.o; nd = R.d; nmeta = R.meta;
+            if ((idx & 7) == 0) atomicAdd(G.cost + R.blk, 1u);                   // cost map: rays per pixel (chain depth), 1 pixel in 8 reports
             if (next) st_stream(B.acc + idx, make_float4(R.acc.x, R.acc.y, R.acc.z, 0.f));
             if (ended) {                                        // radiance -> 8-bit BGR pixel (PATH: mean over samples)
                 const float scale = PATH ? 1.0f / (float)P.spp : 1.0f;
@@ -592,14 +615,14 @@ cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const 
     // The queue variant wins when the frame is long enough to amortise its tail (measured on C3: 4.1 M slots 4.92 vs 5.12 ms,
     // 2.1 M slots 3.10 vs 2.86 ms) and always for path tracing, whose chains run for spp samples (C4 at 1/8: 9.3 vs 10.3 ms).
     const int variant = tune.fused >= 0 ? tune.fused : (path || G.n_slots >= 3000000 ? 2 : 1);
-    const bool have_hist = variant == 1 && tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
+    const bool have_hist = tune.cost_order && m->hist_w == P.width && m->hist_h == P.height && m->hist_rank == P.tile_rank &&
                            m->hist_count == P.tile_count && m->hist_mode == P.mode && m->hist_bs == G.bs;
     info.launches = 0; info.variant = variant;
-    if (have_hist) { k_order<<<1, 1024, 0, st>>>(m->cost, G.nb, m->order); info.launches = 1; }
+    if (have_hist) { k_order<<<1, 1024, 0, st>>>(m->cost, G.nb, G.nbx, tune.cost_order - 1, m->order); info.launches = 1; }
     else MCK(cudaMemsetAsync(m->cost, 0, sizeof(unsigned) * (size_t)G.nb, st));
     G.order = have_hist ? m->order : nullptr;
     G.cost = m->cost;
-    m->hist_w = variant == 1 ? P.width : 0;                              // the queue variant keeps no cost map
+    m->hist_w = P.width;
     m->hist_h = P.height; m->hist_rank = P.tile_rank; m->hist_count = P.tile_count; m->hist_mode = P.mode; m->hist_bs = G.bs;
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -636,8 +659,7 @@ cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const 
         QRing Q;
         Q.org = m->q_org; Q.dir = m->q_dir; Q.ticket = m->q_ticket; Q.ctl = m->q_ctl;
         Q.cap = (unsigned)m->q_cap;
-        MegaGeo GQ = G;
-        GQ.order = nullptr;                                             // no cost map in this variant
+        MegaGeo GQ = G;                                                 // same claim order and cost map as k_mega; cost = rays retired per block
 #define RTB_MEGAQ(PATH, COUNT, MINB) k_megaq<PATH, COUNT, MINB><<<grid, 128, 0, st>>>(tune.queue_keep, (PATH) ? 0 : tune.ring_split, sc, P, GQ, m->head, Q, m->b, img, pitch, aov.prim, aov.inst, aov.t, ctr)
 #define RTB_MEGAQ_MB(PATH) do { if (count) RTB_MEGAQ(PATH, true, 4); else if (mb <= 5) RTB_MEGAQ(PATH, false, 5); \
                                 else if (mb == 6) RTB_MEGAQ(PATH, false, 6); else RTB_MEGAQ(PATH, false, 8); } while (0)

@@ -14,7 +14,8 @@ struct Tune {
     int queue_keep = 28;    // queue variant (fused=2): a warp whose continuing rays number at least this keeps them in their lanes
     int ring_split = 1;     // queue variant: shadow rays and continuation rays go to separate rings (warps start 32 rays of one kind)
     int tail_idle = 2;      // fused kernel, after the last pixel was claimed: retire once this many live lanes are idle
-    int cost_order = 1;     // fused kernel: claim pixel blocks by descending cost of the previous frame (rtb_mega.cu)
+    int cost_order = 2;     // persistent kernels: claim pixel blocks by descending cost of the previous frame: 1 = per block, 2 = per ROW of blocks
+                            // (robust to a camera that pans: rtb_mega.cu k_order), 3 = per block, dilated by two blocks sideways, 0 = off
     int cost_block = 3;     // ... a block being 2^cost_block x 2^cost_block warp tiles of 8 x 4 pixels
     int spec_thr = 4;       // see SceneDev::spec_thr
     int refill_idle = 32;   // queue tracer: refill a warp once this many lanes are idle
