@@ -320,6 +320,8 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    align = torch.zeros(1, dtype=torch.int32, device=dev)
+
     def timed(e2e):
         for i in range(args.warmup):
             step(i, e2e)
@@ -335,7 +337,9 @@ def main():
             if not args.no_flush:
                 flush.fill_(k & 0xFF)                       # L2 flush, outside the timed events
             barrier()
-            ev[k][0].record(stream)
+            if world > 1:
+                dist.all_reduce(align)                       # untimed: lines the ranks' STREAMS up, so that ev0 is the same instant on every
+            ev[k][0].record(stream)                          # device (the host-side barrier above lets them start ~0.1 ms apart)
             step(args.warmup + k, e2e)
             ev[k][1].record(stream)
             barrier()
