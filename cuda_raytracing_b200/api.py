@@ -63,7 +63,8 @@ EXPORTS = ["rtb_context_create", "rtb_context_destroy", "rtb_last_error", "rtb_v
            "rtb_set_materials", "rtb_set_instances", "rtb_update_instance", "rtb_render", "rtb_render_host",
            "rtb_synchronize", "rtb_frame_stats_get", "rtb_debug_math", "rtb_invert_intrinsic", "rtb_invert_lre",
            "rtb_instance_build_inv", "rtb_triangle_init", "rtb_obj_load", "rtb_free",
-           "rtb_frame_alloc_shared", "rtb_frame_free_shared", "rtb_frame_open_shared", "rtb_frame_close_shared", "rtb_push_bands"]
+           "rtb_frame_alloc_shared", "rtb_frame_free_shared", "rtb_frame_open_shared", "rtb_frame_close_shared", "rtb_push_bands",
+           "rtb_frame_signal", "rtb_frame_wait"]
 
 _lib = None
 
@@ -118,6 +119,8 @@ def lib():
     L.rtb_frame_open_shared.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     L.rtb_frame_close_shared.argtypes = [vp, vp]
     L.rtb_push_bands.argtypes = [vp, vp, vp, C.c_size_t, ci, ci, ci, vp]
+    L.rtb_frame_signal.argtypes = [vp, vp, ci, C.c_uint, vp]
+    L.rtb_frame_wait.argtypes = [vp, vp, ci, ci, C.c_uint, vp]
     L.rtb_free.restype = None
     _lib = L
     return L
@@ -325,6 +328,14 @@ class Scene:
 
     def push_bands(self, src_ptr, dst_ptr, pitch, height, rank, world, stream=None):
         _check(lib().rtb_push_bands(self._ctx, src_ptr, dst_ptr, pitch, height, rank, world, stream))
+
+    def frame_signal(self, flags_ptr, slot, value, stream=None):
+        """Enqueue `flags[slot] = value` (system-scope release) behind what this rank put on `stream`."""
+        _check(lib().rtb_frame_signal(self._ctx, flags_ptr, slot, value & 0xffffffff, stream))
+
+    def frame_wait(self, flags_ptr, first, count, value, stream=None):
+        """Enqueue a wait on `stream` until flags[first:first+count] have all reached `value`."""
+        _check(lib().rtb_frame_wait(self._ctx, flags_ptr, first, count, value & 0xffffffff, stream))
 
     def frame_stats(self):
         st = FrameStats()

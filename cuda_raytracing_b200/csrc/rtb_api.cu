@@ -781,6 +781,49 @@ int rtb_push_bands(rtb_context* c, const unsigned char* src, unsigned char* dst,
     return RTB_OK;
 }
 
+// ------------------------------------------------------------------ frame-complete signal over peer memory
+}  // extern "C"
+// One thread publishes `value` in the owner's flag word after everything this stream wrote before it is visible system-wide.
+__global__ void k_frame_signal(unsigned* flags, int slot, unsigned value)
+{
+    __threadfence_system();
+    *((volatile unsigned*)flags + slot) = value;
+    __threadfence_system();
+}
+// Thread i waits until flags[first + i] has reached `value` (wrap-safe compare).  Bounded: ~2 s of spinning sets the
+// frame's overflow flag instead of hanging the device (a missing peer must not cost a GPU).
+__global__ void k_frame_wait(const unsigned* flags, int first, int count, unsigned value, rtb::Counters* ctr)
+{
+    const int i = threadIdx.x;
+    if (i >= count) return;
+    const volatile unsigned* f = (const volatile unsigned*)flags + first + i;
+    const long long t0 = clock64();
+    while ((int)(*f - value) < 0) {
+        __nanosleep(200);
+        if (clock64() - t0 > 4000000000ll) { ctr->overflow = 1; break; }
+    }
+    __threadfence_system();
+}
+extern "C" {
+int rtb_frame_signal(rtb_context* c, unsigned char* flags, int slot, unsigned value, void* stream)
+{
+    if (!c || !flags || slot < 0) return fail(RTB_ERR_INVALID, "rtb_frame_signal: bad argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    k_frame_signal<<<1, 1, 0, (cudaStream_t)stream>>>((unsigned*)flags, slot, value);
+    CU(cudaGetLastError(), "k_frame_signal");
+    return RTB_OK;
+}
+
+int rtb_frame_wait(rtb_context* c, const unsigned char* flags, int first, int count, unsigned value, void* stream)
+{
+    if (!c || !flags || first < 0 || count < 0 || count > 1024) return fail(RTB_ERR_INVALID, "rtb_frame_wait: bad argument");
+    if (count == 0) return RTB_OK;
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    k_frame_wait<<<1, ((count + 31) / 32) * 32, 0, (cudaStream_t)stream>>>((const unsigned*)flags, first, count, value, c->counters_d);
+    CU(cudaGetLastError(), "k_frame_wait");
+    return RTB_OK;
+}
+
 int rtb_synchronize(rtb_context* c)
 {
     if (!c) return fail(RTB_ERR_INVALID, "rtb_synchronize: NULL context");

@@ -80,17 +80,26 @@ class PeerFrame:
         nothing is packed, copied or unpacked afterwards; or
       * mode "push":   renders into a local frame and enqueues ONE strided peer copy of the bands it owns
         (`rtb_push_bands`, a cudaMemcpy2DAsync over NVLink) behind the render kernel.
-    A 4-byte all-reduce on the same stream then tells rank 0 that every band has landed (stream ordered: no host sync).
+    Completion, stream ordered with no host sync, is either
+      * signal "peer": every rank r > 0 stores the frame number into its own 32-bit flag word behind the shared frame
+        (`rtb_frame_signal`: system-scope fence + store, behind its render / push) and rank 0 enqueues a kernel that waits
+        until all world-1 flags reached it (`rtb_frame_wait`) -- no collective on the frame's path; or
+      * signal "nccl": a 4-byte all-reduce on the same stream (what the two-processes-on-one-GPU tests must use: a
+        spinning wait kernel and the kernel it waits for cannot share a GPU).
     `target` is the device pointer this rank passes to `Camera.render_scene`; `frame` (rank 0) is the complete image."""
 
-    def __init__(self, scene, height, pitch, rank, world, device, mode="direct", group=None):
-        assert mode in ("direct", "push")
+    def __init__(self, scene, height, pitch, rank, world, device, mode="direct", group=None, signal="nccl"):
+        assert mode in ("direct", "push") and signal in ("peer", "nccl")
         self.scene, self.h, self.pitch, self.rank, self.world, self.mode, self.group = scene, height, pitch, rank, world, mode, group
+        self.signal, self.frame_no = signal, 0
         self.shared = self.peer = None
         self.flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self.flags_off = ((height * pitch + 255) // 256) * 256          # one 32-bit flag word per rank, behind the frame
         box = [None]
         if rank == 0:
-            self.shared, handle = scene.shared_alloc(height * pitch)
+            self.shared, handle = scene.shared_alloc(self.flags_off + 4 * world + 256)
+            torch.as_tensor(_DevicePointer(self.shared + self.flags_off, (4 * world,)), device=device).zero_()
+            torch.cuda.synchronize(device)
             box[0] = handle
         if world > 1:
             dist.broadcast_object_list(box, src=0, group=group)
@@ -109,7 +118,15 @@ class PeerFrame:
         if self.rank != 0 and self.mode == "push":
             s = stream if stream is not None else torch.cuda.current_stream().cuda_stream
             self.scene.push_bands(self.frame.data_ptr(), self.peer, self.pitch, self.h, self.rank, self.world, s)
-        dist.all_reduce(self.flag, group=self.group)
+        if self.signal == "nccl":
+            dist.all_reduce(self.flag, group=self.group)
+            return self.frame
+        s = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+        self.frame_no += 1
+        if self.rank == 0:
+            self.scene.frame_wait(self.shared + self.flags_off, 1, self.world - 1, self.frame_no, s)
+        else:
+            self.scene.frame_signal(self.peer + self.flags_off, self.rank, self.frame_no, s)
         return self.frame
 
     def close(self):

@@ -157,6 +157,14 @@ RTB_API int rtb_frame_close_shared(rtb_context* ctx, unsigned char* dev_ptr);
 /* copies rows [8b, 8b+8) for every band b with b % tile_count == tile_rank from src to dst (same pitch and height) */
 RTB_API int rtb_push_bands(rtb_context* ctx, const unsigned char* src, unsigned char* dst, size_t pitch, int height,
                            int tile_rank, int tile_count, void* stream);
+/* Completion signal over the same peer memory, so that no collective sits on the frame's path: `flags` points at 32-bit words
+ * in memory every rank can reach (tiles.py keeps them behind the shared frame).  rtb_frame_signal enqueues, behind the caller's
+ * render / push on `stream`, a system-scope fence and the store flags[slot] = value; rtb_frame_wait enqueues on the owner's
+ * stream a kernel that returns once flags[first .. first+count) have all reached `value` (wrap-safe, so `value` is simply
+ * the frame number).  The wait is bounded (about two seconds): a peer that never signals sets rtb_frame_stats.overflow
+ * instead of hanging the device.  Ranks must be separate GPUs (a spinning kernel and its producer cannot share one). */
+RTB_API int rtb_frame_signal(rtb_context* ctx, unsigned char* flags, int slot, unsigned value, void* stream);
+RTB_API int rtb_frame_wait(rtb_context* ctx, const unsigned char* flags, int first, int count, unsigned value, void* stream);
 /* Evaluates a device math helper on n host floats (tests): what = 0 atanf with host-libm bits (raycast.cu:170),
  * 1 Q_rsqrt (utils.hpp:12-27). */
 RTB_API int rtb_debug_math(rtb_context* ctx, int what, const float* in_host, float* out_host, int n);

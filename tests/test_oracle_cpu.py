@@ -252,6 +252,7 @@ def test_cabi_rejects_null_arguments_without_a_device(rtb):
         "rtb_synchronize": (None,), "rtb_frame_stats_get": (None, None), "rtb_frame_alloc_shared": (None, 0, None, None),
         "rtb_frame_free_shared": (None, None), "rtb_frame_open_shared": (None, None, None), "rtb_frame_close_shared": (None, None),
         "rtb_push_bands": (None, None, None, 0, 0, 0, 1, None), "rtb_debug_math": (None, 0, None, None, 0),
+        "rtb_frame_signal": (None, None, 0, 0, None), "rtb_frame_wait": (None, None, 0, 0, 0, None),
     }
     for name, args in calls.items():
         assert getattr(L, name)(*args) == -1, name

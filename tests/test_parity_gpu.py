@@ -487,15 +487,23 @@ def test_tile_partition_is_byte_identical(rtb, mode, depth):
 
 # ------------------------------------------------------------------ frame exchange over peer memory: 2 processes (one GPU is enough: CUDA IPC
 # works between processes on the same device; gloo carries the handle and the completion signal, NCCL refuses two ranks on one GPU)
+def tiles_pointer(ptr, nbytes):
+    from cuda_raytracing_b200 import tiles
+    return tiles._DevicePointer(ptr, (nbytes,))
+
+
 PEER_WORKER = r'''
 import os, sys, numpy as np, torch, torch.distributed as dist
 sys.path.insert(0, sys.argv[1])
 from cuda_raytracing_b200 import api, tiles, synth
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 dist.init_process_group("gloo")
-torch.cuda.set_device(0)
+signal = os.environ.get("RTB_TEST_SIGNAL", "nccl")
+devno = rank if signal == "peer" else 0                    # flag-word signalling needs one GPU per rank (a spinning wait kernel)
+dev = "cuda:%d" % devno
+torch.cuda.set_device(devno)
 tris = synth.bumpy_sphere(24, 48, ground=True)
-s = api.Scene(0)
+s = api.Scene(devno)
 s.add_material(api.Material(albedo=(0.2, 0.5, 0.9), metallic=0.5))
 s.add_mesh(api.MeshPrimitive(tris))
 s.add_mesh_instance(api.MeshInstance(0, 0))
@@ -507,18 +515,22 @@ cam.pose = np.array((0.0, -2.6, 1.6, 0.0, -0.22, 0.0), np.float32)
 for mode, depth in ((1, 0), (2, 3)):
     cam.mode, cam.max_depth = mode, depth
     for how in ("direct", "push"):
-        pf = tiles.PeerFrame(s, H, pitch, rank, world, "cuda:0", mode=how)
+        pf = tiles.PeerFrame(s, H, pitch, rank, world, dev, mode=how, signal=signal)
         cam.tile_rank, cam.tile_count = rank, world
-        for _ in range(2):
+        for _ in range(3):
             cam.render_scene(s, pf.target, pitch)
             pf.gather()
+        if rank == 0 and signal == "peer":                        # rank 0's stream alone must be enough: no barrier before the read
+            got = pf.frame.cpu().numpy().copy()
         torch.cuda.synchronize(); dist.barrier()
         if rank == 0:
-            got = pf.frame.cpu().numpy().copy()
+            if signal != "peer":
+                got = pf.frame.cpu().numpy().copy()
             cam.tile_rank, cam.tile_count = 0, 1
-            ref = torch.zeros((H, pitch), dtype=torch.uint8, device="cuda:0")
+            ref = torch.zeros((H, pitch), dtype=torch.uint8, device=dev)
             cam.render_scene(s, ref.data_ptr(), pitch, synchronize=True)
             assert got.any() and np.array_equal(got, ref.cpu().numpy()), (mode, how)
+            s.frame_stats()                                       # raises if a wait timed out
         dist.barrier()
         pf.close()
 if rank == 0:
@@ -536,6 +548,48 @@ def test_peer_frame_exchange_two_processes(rtb, tmp_path):
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                           "--master-port", "29631", str(w), root], capture_output=True, text=True, timeout=300)
     assert "PEER_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-3000:]
+
+
+def test_peer_frame_flag_signal_two_gpus(rtb, tmp_path):
+    """The same exchange with the completion carried by flag words in peer memory (rtb_frame_signal / rtb_frame_wait) instead of a
+    collective: needs one GPU per rank."""
+    import subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("flag-word completion needs two GPUs")
+    w = tmp_path / "peer_worker.py"
+    w.write_text(PEER_WORKER)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                          "--master-port", "29633", str(w), root], capture_output=True, text=True, timeout=300,
+                         env=dict(os.environ, RTB_TEST_SIGNAL="peer"))
+    assert "PEER_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-3000:]
+
+
+def test_frame_signal_and_wait_on_one_stream(rtb):
+    """rtb_frame_signal then rtb_frame_wait on one stream: the wait returns at once for values already reached (wrap-safe compare),
+    and a value nobody publishes ends in the bounded time-out that raises the frame's overflow flag instead of hanging."""
+    import torch
+    s = rtb.Scene(0)
+    ptr, _ = s.shared_alloc(4096)
+    flags = torch.as_tensor(tiles_pointer(ptr, 4096), device="cuda:0")
+    flags.zero_()
+    torch.cuda.synchronize()
+    for frame_no in (1, 2, 0xffffffff, 0x100000003):               # the last one wraps to 3: still "after" 0xffffffff
+        for slot in (1, 2, 3):
+            s.frame_signal(ptr, slot, frame_no)
+        s.frame_wait(ptr, 1, 3, frame_no)
+        s.frame_wait(ptr, 1, 3, frame_no - 1)
+        s.synchronize()
+        words = flags.view(torch.int32).cpu().numpy().view(np.uint32)
+        assert list(words[:5]) == [0, frame_no & 0xffffffff, frame_no & 0xffffffff, frame_no & 0xffffffff, 0]
+    s.frame_stats()
+    s.frame_wait(ptr, 1, 3, 9)                                      # never published: ~2 s, then the overflow flag
+    s.synchronize()
+    with pytest.raises(rtb.RtbError):
+        s.frame_stats()
+    del flags
+    s.shared_free(ptr)
+    s.close()
 
 
 # ------------------------------------------------------------------ full-size configs: the WHOLE frame against the oracle and against the
