@@ -58,13 +58,15 @@ class FrameStats(C.Structure):
 
 assert C.sizeof(CInstance) == 104 and C.sizeof(CMaterial) == 48 and C.sizeof(Lre) == 24
 
+NOALLOC_MAX_SLOTS = 131072        # RTB_NOALLOC_MAX_SLOTS (include/rtb200.h)
+
 EXPORTS = ["rtb_context_create", "rtb_context_destroy", "rtb_last_error", "rtb_version", "rtb_set_option",
            "rtb_mesh_create", "rtb_mesh_rebuild", "rtb_mesh_rebuild_async", "rtb_mesh_commit", "rtb_mesh_info_get", "rtb_mesh_read", "rtb_mesh_destroy", "rtb_texture_upload",
            "rtb_set_materials", "rtb_set_instances", "rtb_update_instance", "rtb_render", "rtb_render_host",
            "rtb_synchronize", "rtb_frame_stats_get", "rtb_debug_math", "rtb_invert_intrinsic", "rtb_invert_lre",
            "rtb_instance_build_inv", "rtb_triangle_init", "rtb_obj_load", "rtb_free",
            "rtb_frame_alloc_shared", "rtb_frame_free_shared", "rtb_frame_open_shared", "rtb_frame_close_shared", "rtb_push_bands",
-           "rtb_frame_signal", "rtb_frame_wait"]
+           "rtb_frame_signal", "rtb_frame_wait", "rtb_render_noalloc"]
 
 _lib = None
 
@@ -100,6 +102,7 @@ def lib():
     L.rtb_set_instances.argtypes = [vp, vp, ci]
     L.rtb_update_instance.argtypes = [vp, ci, vp]
     L.rtb_render.argtypes = [vp, C.POINTER(RenderParams), vp, C.c_size_t, C.POINTER(Aovs), vp]
+    L.rtb_render_noalloc.argtypes = [vp, C.POINTER(RenderParams), vp, C.c_size_t, C.POINTER(Aovs), vp]
     L.rtb_render_host.argtypes = [vp, C.POINTER(RenderParams), vp, C.c_size_t, C.POINTER(Aovs)]
     L.rtb_synchronize.argtypes = [vp]
     L.rtb_frame_stats_get.argtypes = [vp, C.POINTER(FrameStats)]
@@ -377,6 +380,15 @@ class Camera:
         p = self.params()
         a = Aovs(*aovs) if aovs is not None else None
         _check(lib().rtb_render(scene._ctx, C.byref(p), img_ptr, pitch, C.byref(a) if a is not None else None, stream))
+        if synchronize:
+            scene.synchronize()
+
+    def render_scene_noalloc(self, scene, img_ptr, pitch, synchronize=False, aovs=None, stream=None):
+        """rtb_render_noalloc: the REFLECT / PATH frame of render_scene with the kernel's scratch in the library's static device
+        array -- no allocation anywhere on the call; frames above NOALLOC_MAX_SLOTS pixels are rejected (RtbError)."""
+        p = self.params()
+        a = Aovs(*aovs) if aovs is not None else None
+        _check(lib().rtb_render_noalloc(scene._ctx, C.byref(p), img_ptr, pitch, C.byref(a) if a is not None else None, stream))
         if synchronize:
             scene.synchronize()
 

@@ -49,6 +49,14 @@ struct MeshRec {
     int cut_serial = 0;             // bumped whenever the cut changes (instances remember the one they were packed against)
 };
 
+namespace rtb {
+cudaError_t mega_static_setup(int device);                            // rtb_mega.cu: the static scratch of rtb_render_noalloc
+size_t mega_static_bytes();
+bool mega_static_fits(const Tune& tune, const FrameParams& P, long long* slots, long long* pixels);
+cudaError_t launch_mega_static(const Tune& tune, LaunchInfo& info, int device, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
+                               const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st);
+}
+
 struct rtb_context {
     int device = 0;
     std::vector<MeshRec> meshes;
@@ -110,6 +118,7 @@ int rtb_context_create(int device, rtb_context** out)
     CU(cudaEventCreate(&c->ev0), "cudaEventCreate");
     CU(cudaEventCreate(&c->ev1), "cudaEventCreate");
     CU(cudaEventCreateWithFlags(&c->frame_done, cudaEventDisableTiming), "cudaEventCreate");
+    rtb::mega_static_setup(device);     // address of rtb_render_noalloc's static scratch on this device; a failure is reported by that call
     *out = c;
     return RTB_OK;
 }
@@ -666,6 +675,52 @@ int rtb_render(rtb_context* c, const rtb_render_params* p, unsigned char* img, s
     if (!c || !p || !img) return fail(RTB_ERR_INVALID, "rtb_render: NULL argument");
     CU(cudaSetDevice(c->device), "cudaSetDevice");
     return render_impl(c, p, img, pitch, aovs, (cudaStream_t)stream);
+}
+
+// No allocation on this path: no cudaMalloc / cudaFree, no table upload, no std::vector -- a scene that still needs any of that
+// is refused (RTB_ERR_STATE) and the caller renders one frame through rtb_render first.
+int rtb_render_noalloc(rtb_context* c, const rtb_render_params* p, unsigned char* img, size_t pitch, const rtb_aovs* aovs, void* stream)
+{
+    if (!c || !p || !img) return fail(RTB_ERR_INVALID, "rtb_render_noalloc: NULL argument");
+    CU(cudaSetDevice(c->device), "cudaSetDevice");
+    if (p->mode != RTB_MODE_REFLECT && p->mode != RTB_MODE_PATH)
+        return fail(RTB_ERR_INVALID, "rtb_render_noalloc: only RTB_MODE_REFLECT / RTB_MODE_PATH use scratch memory; modes 0 / 1 allocate nothing in rtb_render");
+    FrameParams P;
+    int rc = make_frame(p, P); if (rc != RTB_OK) return rc;
+    if (pitch < (size_t)p->width * 3) return fail(RTB_ERR_INVALID, "rtb_render_noalloc: pitch smaller than a row");
+    long long slots = 0, pixels = 0;
+    if (!rtb::mega_static_fits(c->tune, P, &slots, &pixels))
+        return fail(RTB_ERR_INVALID, "rtb_render_noalloc: frame of " + std::to_string(p->width) + " x " + std::to_string(p->height) + " needs " +
+                                         std::to_string(pixels) + " pixels and " + std::to_string(slots) + " pixel slots, the static scratch holds " +
+                                         std::to_string((long long)RTB_NOALLOC_MAX_SLOTS) + " (RTB_NOALLOC_MAX_SLOTS); use rtb_render");
+    if (!c->tlas.nodes) return fail(RTB_ERR_STATE, "rtb_render_noalloc: no instances set (call rtb_set_instances)");
+    if (c->tlas_dirty || c->mesh_table_dirty || !c->meshes_d)
+        return fail(RTB_ERR_STATE, "rtb_render_noalloc: the scene changed since the last frame and its device tables are stale; "
+                                   "render one frame with rtb_render first (that call may allocate)");
+    int deepest = 0;
+    for (const auto& in : c->instances_h) {
+        if (!c->meshes[in.mesh_index].alive) return fail(RTB_ERR_STATE, "rtb_render_noalloc: an instance refers to a destroyed mesh");
+        deepest = std::max(deepest, c->meshes[in.mesh_index].bvh.depth);
+    }
+    if ((c->instances_h.size() > 1 ? 3 * c->tlas.depth + 1 : 0) + 3 * deepest + 2 > STACK_CAP)
+        return fail(RTB_ERR_OVERFLOW, "rtb_render_noalloc: the scene's trees need a deeper traversal stack than the kernels have");
+    SceneDev sc;
+    sc.tlas_nodes = c->tlas.nodes; sc.tlas_index = (const int*)c->tlas.order; sc.inst = c->inst_d; sc.meshes = c->meshes_d;
+    sc.materials = c->materials_d; sc.num_instances = (int)c->instances_h.size(); sc.num_materials = (int)c->materials_h.size();
+    sc.tlas_extent = bounds_extent(c->tlas.bounds, sc.num_instances);
+    sc.top_blas = nullptr; sc.top_tlas_n = sc.top_blas_n = 0;           // no top levels staged in shared memory (only a placement choice)
+    sc.spec_thr = c->tune.spec_thr;
+    rtb_aovs a = { nullptr, nullptr, nullptr };
+    if (aovs) a = *aovs;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaMemsetAsync(c->counters_d, 0, sizeof(Counters), st), "counters reset");
+    cudaError_t e = rtb::launch_mega_static(c->tune, c->last_info, c->device, sc, P, img, pitch, a, c->counters_d, c->opt_counters != 0, st);
+    if (e != cudaSuccess)
+        return fail(RTB_ERR_CUDA, std::string("rtb_render_noalloc: ") + cudaGetErrorString(e) +
+                                      (e == cudaErrorNotReady ? " (static scratch address not set up for this device)" : ""));
+    c->last_launches = c->last_info.launches;
+    CU(cudaEventRecord(c->frame_done, st), "frame event");
+    return RTB_OK;
 }
 
 int rtb_render_host(rtb_context* c, const rtb_render_params* p, unsigned char* img_host, size_t pitch_host, const rtb_aovs* aovs_host)

@@ -17,6 +17,7 @@
 // traversal writes on every accepted candidate, and the shadow ray's pending Lambert term + continuation ray.
 #include "rtb_wave_common.cuh"
 #include <algorithm>
+#include <mutex>
 
 namespace rtb {
 
@@ -676,6 +677,114 @@ cudaError_t launch_mega(const Tune& tune, LaunchInfo& info, void** state, const 
                                                                                      aov.prim, aov.inst, aov.t, ctr); } while (0)
 #define RTB_MEGA_MB(PATH) do { if (count) RTB_MEGA(PATH, true, 4); else if (mb == 4) RTB_MEGA(PATH, false, 4); else if (mb == 5) RTB_MEGA(PATH, false, 5); \
                                else if (mb == 6) RTB_MEGA(PATH, false, 6); else RTB_MEGA(PATH, false, 8); } while (0)
+    if (path) RTB_MEGA_MB(true); else RTB_MEGA_MB(false);
+    info.launches += 2;
+    MCK(cudaGetLastError());
+    return launch_emit_frame<true>(P, 1.0f, m->b.pix, nullptr, img, pitch, st);
+}
+
+// ------------------------------------------------------------------ the same kernel with its scratch in a static device array
+// (rtb_render_noalloc, include/rtb200.h): for callers that must not allocate -- CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc.  Everything k_mega keeps per pixel slot (eight float4 arrays), the packed pixels k_emit_frame reads, the
+// per-block cost words and the slot counter are carved out of g_static_scratch below, which every GPU that loads the library holds
+// until the process exits.  All calls share it: calls that overlap on one GPU race (see the header).
+constexpr int STATIC_MAX_SLOTS = RTB_NOALLOC_MAX_SLOTS;           // pixel slots (the frame's own bands padded to claim blocks)
+constexpr int STATIC_MAX_PIXELS = RTB_NOALLOC_MAX_SLOTS;          // width * height of the whole frame (pix is indexed y * width + x)
+constexpr size_t STATIC_OFF_PIX = sizeof(float4) * 8 * (size_t)STATIC_MAX_SLOTS;
+constexpr size_t STATIC_OFF_COST = STATIC_OFF_PIX + sizeof(unsigned) * (size_t)STATIC_MAX_PIXELS;
+constexpr size_t STATIC_OFF_HEAD = STATIC_OFF_COST + sizeof(unsigned) * (size_t)(STATIC_MAX_SLOTS / 32);    // a block has >= 32 slots
+constexpr size_t STATIC_BYTES = STATIC_OFF_HEAD + 256;
+static_assert(STATIC_OFF_PIX % 256 == 0 && STATIC_OFF_COST % 256 == 0 && STATIC_OFF_HEAD % 256 == 0, "sub-arrays stay 256-byte aligned");
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_BYTES];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+constexpr int STATIC_MAX_DEVICES = 64;
+static unsigned char* g_static_base[STATIC_MAX_DEVICES] = {};
+static cudaError_t g_static_status[STATIC_MAX_DEVICES] = {};
+static bool g_static_done[STATIC_MAX_DEVICES] = {};
+static std::mutex g_static_mutex;
+
+size_t mega_static_bytes() { return STATIC_BYTES; }
+
+cudaError_t mega_static_setup(int device)
+{
+    if (device < 0 || device >= STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (g_static_done[device]) return g_static_status[device];
+    int cur = -1;
+    cudaError_t e = cudaGetDevice(&cur);
+    if (e == cudaSuccess && cur != device) e = cudaErrorInvalidDevice;      // the caller makes the device current first
+    void* ptr = nullptr;
+    if (e == cudaSuccess) e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e == cudaSuccess && (!ptr || ((uintptr_t)ptr & 255u))) e = cudaErrorInvalidSymbol;
+    g_static_base[device] = e == cudaSuccess ? (unsigned char*)ptr : nullptr;
+    g_static_status[device] = e;
+    g_static_done[device] = true;
+    return e;
+}
+
+// Slot / pixel need of a frame for the static variant; false when it does not fit (slots and pixels are reported either way).
+bool mega_static_fits(const Tune& tune, const FrameParams& P, long long* slots, long long* pixels)
+{
+    const int bands = (P.height + BAND_ROWS - 1) / BAND_ROWS;
+    const int my_bands = std::max(0, (bands - P.tile_rank + P.tile_count - 1) / P.tile_count);
+    const int bs = std::max(0, std::min(tune.cost_block, 3)), bt = 1 << bs;
+    const long long tiles_x = (P.width + 7) / 8, tile_rows = (long long)my_bands * (BAND_ROWS / 4);
+    const long long nb = ((tiles_x + bt - 1) / bt) * ((tile_rows + bt - 1) / bt);
+    *slots = nb * (32ll << (2 * bs));
+    *pixels = (long long)P.width * P.height;
+    return *slots <= STATIC_MAX_SLOTS && *pixels <= STATIC_MAX_PIXELS;
+}
+
+// launch_mega's k_mega branch (lane-owned chains) with MegaState pointing into the static array: no allocation, no cost history.
+cudaError_t launch_mega_static(const Tune& tune, LaunchInfo& info, int device, const SceneDev& sc, const FrameParams& P, unsigned char* img, size_t pitch,
+                               const rtb_aovs& aov, Counters* ctr, bool count, cudaStream_t st)
+{
+    if (device < 0 || device >= STATIC_MAX_DEVICES || !g_static_done[device]) return cudaErrorNotReady;
+    if (g_static_status[device] != cudaSuccess) return g_static_status[device];
+    long long slots = 0, pixels = 0;
+    if (!mega_static_fits(tune, P, &slots, &pixels)) return cudaErrorInvalidValue;
+    const bool path = P.mode == RTB_MODE_PATH;
+    const int bands = (P.height + BAND_ROWS - 1) / BAND_ROWS;
+    const int my_bands = (bands - P.tile_rank + P.tile_count - 1) / P.tile_count;
+    info.launches = 0; info.variant = 1;
+    if (my_bands <= 0) return cudaSuccess;
+    MegaGeo G;
+    G.tiles_x = (P.width + 7) / 8;
+    G.tile_rows = my_bands * (BAND_ROWS / 4);
+    G.bs = std::max(0, std::min(tune.cost_block, 3));
+    const int bt = 1 << G.bs;
+    G.nbx = (G.tiles_x + bt - 1) / bt;
+    G.nb = G.nbx * ((G.tile_rows + bt - 1) / bt);
+    G.n_slots = G.nb * (32 << (2 * G.bs));
+    if (P.max_depth > 126 || P.spp >= (1 << 24)) return cudaErrorInvalidValue;
+    unsigned char* base = g_static_base[device];
+    MegaState ms; MegaState* m = &ms;
+    float4** bufs[] = { &m->b.acc, &m->b.thr, &m->b.hit0, &m->b.hit1, &m->b.sp0, &m->b.sp1, &m->b.cont_o, &m->b.cont_d };
+    for (int i = 0; i < 8; i++) *bufs[i] = (float4*)(base + sizeof(float4) * (size_t)STATIC_MAX_SLOTS * i);
+    m->b.pix = (unsigned*)(base + STATIC_OFF_PIX);
+    m->cost = (unsigned*)(base + STATIC_OFF_COST);
+    m->head = (int*)(base + STATIC_OFF_HEAD);
+    // what must start at zero: the per-block cost words (here) and the slot counter (k_frame_begin); every other word of the
+    // scratch is written by the frame before it is read, so the last call's contents do not matter
+    MCK(cudaMemsetAsync(m->cost, 0, sizeof(unsigned) * (size_t)G.nb, st));
+    G.order = nullptr;
+    G.cost = m->cost;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (path && (aov.prim || aov.inst || aov.t)) {
+        FrameParams Q = P; Q.mode = RTB_MODE_REFERENCE;                 // first-hit AOVs from the un-jittered centre ray, as in launch_mega
+        MCK(launch_render(tune, sc, Q, img, pitch, aov, ctr, count, st));
+        info.launches++;
+    }
+    const int mb = tune.trace_minb <= 4 ? 4 : (tune.trace_minb == 5 ? 5 : (tune.trace_minb == 6 ? 6 : 8));
+    const int ri = tune.refill_idle;
+    const int grid = std::min(sms * (count ? 4 : mb), (G.n_slots + 127) / 128);
+    const bool smem = false;                                            // no staged top levels: SceneDev comes without them here
+    const size_t shb = 0;
+    k_frame_begin<<<1, 128, 0, st>>>(m->head, nullptr, 0);
+    info.launches++;
     if (path) RTB_MEGA_MB(true); else RTB_MEGA_MB(false);
     info.launches += 2;
     MCK(cudaGetLastError());

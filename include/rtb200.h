@@ -140,6 +140,21 @@ RTB_API int rtb_render(rtb_context* ctx, const rtb_render_params* p, unsigned ch
  * given as HOST pointers) to the caller's host memory and synchronises. */
 RTB_API int rtb_render_host(rtb_context* ctx, const rtb_render_params* p, unsigned char* img_host, size_t pitch_host,
                             const rtb_aovs* aovs_host);
+/* The same frame as rtb_render for RTB_MODE_REFLECT / RTB_MODE_PATH, for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  This entry point has no counterpart in the reference.
+ * It calls no cudaMalloc, cudaFree or allocating library routine: the fused
+ * kernel's per-pixel scratch lives in a static device array of RTB_NOALLOC_MAX_SLOTS pixel slots (17 318 144 bytes, about 16.5 MiB, that every GPU
+ * which loads the library holds until the process exits).  Limits: width * height <= RTB_NOALLOC_MAX_SLOTS, and the rank's own
+ * bands padded to claim blocks (64 x 32 pixels at the default "cost_block" 3) <= RTB_NOALLOC_MAX_SLOTS -- e.g. 320 x 240,
+ * 448 x 256, 512 x 256; larger frames are rejected with RTB_ERR_INVALID and a message naming both numbers.  Modes 0 / 1 need
+ * no scratch: use rtb_render.  The scene must be ready: at least one rtb_render / rtb_render_host after the last
+ * rtb_set_instances / rtb_update_instance / mesh call (those upload tables and may allocate), otherwise RTB_ERR_STATE.
+ * Pixels and AOVs are bit-identical to rtb_render's.  Every call shares the one array, which keeps the last call's contents
+ * (the call clears the words that must start at zero); calls of one process that overlap on one GPU -- two streams, two
+ * contexts on the same device -- race on it and produce garbage: serialise them (one stream, or events between streams). */
+#define RTB_NOALLOC_MAX_SLOTS 131072
+RTB_API int rtb_render_noalloc(rtb_context* ctx, const rtb_render_params* p, unsigned char* img, size_t pitch,
+                               const rtb_aovs* aovs, void* stream);
 RTB_API int rtb_synchronize(rtb_context* ctx);                                            /* cudaDeviceSynchronize, kernel.cu:279 */
 RTB_API int rtb_frame_stats_get(rtb_context* ctx, rtb_frame_stats* out);
 /* ---- multi-GPU frame exchange over peer memory (one process per GPU on one NVSwitch node; no counterpart in the

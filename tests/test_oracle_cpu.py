@@ -249,6 +249,7 @@ def test_cabi_rejects_null_arguments_without_a_device(rtb):
         "rtb_mesh_info_get": (None, 0, None), "rtb_mesh_destroy": (None, 0), "rtb_mesh_read": (None, 0, 0, None, 0),
         "rtb_texture_upload": (None, None, 0, 0, None, None), "rtb_set_materials": (None, None, 0), "rtb_set_instances": (None, None, 0),
         "rtb_update_instance": (None, 0, None), "rtb_render": (None, None, None, 0, None, None), "rtb_render_host": (None, None, None, 0, None),
+        "rtb_render_noalloc": (None, None, None, 0, None, None),
         "rtb_synchronize": (None,), "rtb_frame_stats_get": (None, None), "rtb_frame_alloc_shared": (None, 0, None, None),
         "rtb_frame_free_shared": (None, None), "rtb_frame_open_shared": (None, None, None), "rtb_frame_close_shared": (None, None),
         "rtb_push_bands": (None, None, None, 0, 0, 0, 1, None), "rtb_debug_math": (None, 0, None, None, 0),
