@@ -235,7 +235,7 @@ def main():
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--ref-cuda-as-shipped", action="store_true", help="also time the reference kernel exactly as shipped (UB Q_rsqrt), +25 s")
     ap.add_argument("--no-flush", action="store_true")
-    ap.add_argument("--signal", default="nccl", choices=["peer", "nccl"],
+    ap.add_argument("--completion", default="nccl", choices=["peer", "nccl"],
                     help="N>1, peer exchange: how rank 0 learns that every band has landed (flag words in peer memory, or a 4-byte all-reduce)")
     ap.add_argument("--exchange", default="direct", choices=["direct", "push", "nccl"],
                     help="N>1: how the bands reach rank 0 (tiles.PeerFrame direct stores / peer copy, or the NCCL gather)")
@@ -282,7 +282,7 @@ def main():
     from cuda_raytracing_b200 import tiles
     if world > 1 and args.exchange != "nccl":
         # frame exchange over NVLink peer memory: ranks > 0 write their bands into rank 0's frame (tiles.PeerFrame)
-        fg = tiles.PeerFrame(scene, H, pitch, rank, world, dev, mode=args.exchange, signal=args.signal)
+        fg = tiles.PeerFrame(scene, H, pitch, rank, world, dev, mode=args.exchange, signal=args.completion)
         frame, target = fg.frame, fg.target
     else:
         frame = torch.zeros((H, pitch), dtype=torch.uint8, device=dev)
@@ -487,7 +487,7 @@ def main():
                     details=dict(parallelism="image bands of %d rows interleaved over %d GPU(s), scene replicated, bands to rank 0: %s" % (
                                      api.BAND_ROWS, world, {"direct": "kernel stores into rank 0's frame over NVLink peer memory",
                                                             "push": "one strided peer copy per rank over NVLink", "nccl": "NCCL gather"}[args.exchange] if world > 1 else "-"),
-                                 signal=(args.signal if world > 1 and args.exchange != "nccl" else "-"),
+                                 signal=(args.completion if world > 1 and args.exchange != "nccl" else "-"),
                                  l2="flushed between steps with a 256 MiB write (untimed)" if not args.no_flush else "not flushed",
                                  rays_per_frame=rays / args.steps, blas=dict(nodes=info["num_nodes"], leaves=info["num_leaves"], depth=info["depth"],
                                                                           build_ms=info["build_ms"], bytes=info["device_bytes"])),

@@ -45,6 +45,8 @@ REPORT = []            # one record per compare(): written to gpurun_out/parity_
 def parity_report():
     yield
     import json
+    if not REPORT:                      # a -k selection without comparisons must not replace a full run's report
+        return
     out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
     os.makedirs(out, exist_ok=True)
     tot = dict(comparisons=len(REPORT), pixels=sum(r["pixels"] for r in REPORT), id_mismatches=sum(r["id_mismatches"] for r in REPORT),
