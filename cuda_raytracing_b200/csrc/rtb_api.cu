@@ -87,6 +87,7 @@ struct rtb_context {
     float last_ms = 0.f;
     int last_launches = 0;
     int opt_counters = 0, opt_leaf = 8, opt_key_bits = 0;
+    int opt_build_fused = 1;       // option "build_fused": fit + chunk-local collapse in one kernel (rtb_build.cu k_fit_collapse)
     rtb::Tune tune;                // kernel tuning knobs of THIS context (rtb_set_option)
     float sah_node_cost = 1.0f;    // option "sah_node" (permille)
     rtb::LaunchInfo last_info;
@@ -176,6 +177,7 @@ int rtb_set_option(rtb_context* c, const char* name, int value)
     else if (n == "leaf_size") c->opt_leaf = std::max(1, std::min(value, (int)MAX_LEAF));
     else if (n == "key_bits") c->opt_key_bits = value;
     else if (n == "sah_node") c->sah_node_cost = 0.001f * (float)std::max(1, std::min(value, 100000));
+    else if (n == "build_fused") c->opt_build_fused = value != 0;
     else if (n == "inst_cut") { c->opt_inst_cut = std::max(1, std::min(value, 1024)); c->tlas_dirty = !c->instances_h.empty(); }
     else if (n == "fused") c->tune.fused = value;
     else if (n == "cost_order") c->tune.cost_order = value;
@@ -219,7 +221,7 @@ static int build_mesh(rtb_context* c, MeshRec& m, const rtb_triangle* tris, int 
     }
     CU(cudaEventRecord(c->ev0, st), "event");
     int key_bits = c->opt_key_bits ? c->opt_key_bits : (n > (1 << 21) ? 64 : 32);
-    CU(build_bvh(tris_d, bmin, bmax, n, c->opt_leaf, key_bits, c->sah_node_cost, m.bvh, c->ws, st, m.tri_rec, m.uvs, c->ev1), "build_bvh");
+    CU(build_bvh(tris_d, bmin, bmax, n, c->opt_leaf, key_bits, c->sah_node_cost, m.bvh, c->ws, st, m.tri_rec, m.uvs, c->ev1, nullptr, c->opt_build_fused), "build_bvh");
     CU(cudaEventSynchronize(c->ev1), "build sync");
     float ms = 0.f;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
@@ -305,7 +307,7 @@ int rtb_mesh_rebuild_async(rtb_context* c, int id, const rtb_triangle* tris, int
     float4* bmax = c->stage_async.take<float4>(nn);
     CU(cudaEventRecord(c->ev_b0, st), "event");
     const int key_bits = c->opt_key_bits ? c->opt_key_bits : (n > (1 << 21) ? 64 : 32);
-    CU(build_bvh(tris, bmin, bmax, n, c->opt_leaf, key_bits, c->sah_node_cost, b.bvh, c->ws_async, st, b.tri_rec, b.uvs, b.built, b.counters_h), "build_bvh");
+    CU(build_bvh(tris, bmin, bmax, n, c->opt_leaf, key_bits, c->sah_node_cost, b.bvh, c->ws_async, st, b.tri_rec, b.uvs, b.built, b.counters_h, c->opt_build_fused), "build_bvh");
     b.n = n; b.pending = true;
     return RTB_OK;
 }
@@ -428,13 +430,19 @@ static int mesh_cut(rtb_context* c, MeshRec& m, int budget)
         }
         for (int k = 0; k < 3; k++) m.cut.push_back(b[k + 3] + (b[k] - m.cut[k]));
     } else if (m.n > 0 && finite && budget > 1 && m.bvh.num_nodes >= 1) {
-        const int K = std::min(m.bvh.num_nodes, 85);
-        std::vector<float4> nd((size_t)K * NODE_F4);
-        CU(cudaMemcpy(nd.data(), m.bvh.nodes, sizeof(float4) * nd.size(), cudaMemcpyDeviceToHost), "read top BLAS levels");
+        // the nodes of the top levels are not contiguous (fused build: only node 0 is at a known place), so they are fetched one
+        // by one as the cut opens them: at most 85 small copies, once per build of a static mesh
+        const int K = m.bvh.num_nodes;
+        float4 nd[NODE_F4];
+        int fetched = 0;
+        cudaError_t fetch_err = cudaSuccess;
         struct Box { float lo[3], hi[3]; int ref; };
         std::vector<Box> open, done;                      // open: FIFO (head index), so the cut is opened level by level
         auto children = [&](int node) {
-            const float* f = (const float*)&nd[(size_t)node * NODE_F4];
+            cudaError_t e = cudaMemcpy(nd, m.bvh.nodes + (size_t)node * NODE_F4, sizeof nd, cudaMemcpyDeviceToHost);
+            if (e != cudaSuccess) { fetch_err = e; return; }
+            fetched++;
+            const float* f = (const float*)nd;
             for (int k = 0; k < 4; k++) {
                 int ref; memcpy(&ref, f + 24 + k, 4);
                 if (ref == EMPTY_REF) continue;
@@ -448,9 +456,10 @@ static int mesh_cut(rtb_context* c, MeshRec& m, int budget)
         size_t head = 0;
         while (head < open.size()) {
             const Box x = open[head++];
-            if (x.ref >= 0 && x.ref < K && done.size() + (open.size() - head) + 4 <= (size_t)budget) children(x.ref);
+            if (x.ref >= 0 && x.ref < K && fetched < 85 && done.size() + (open.size() - head) + 4 <= (size_t)budget) children(x.ref);
             else done.push_back(x);
         }
+        CU(fetch_err, "read top BLAS levels");
         for (const Box& x : done)
             for (int a = 0; a < 3; a++) finite = finite && std::isfinite(x.lo[a]) && std::isfinite(x.hi[a]) && x.lo[a] <= x.hi[a];
         if (finite && !done.empty()) {

@@ -34,10 +34,12 @@ struct BvhResult {
 // With `tri_rec`/`uvs` as well, the 64-byte triangle records and the uvs are written in leaf order (k_emit_tris).
 // `done` (optional) is recorded after the last kernel.  Asynchronous on `st` except for one small read-back of the build
 // counters at the end.
+// build_fused: fit + collapse of everything below the 256-leaf chunks in one kernel (k_fit_collapse); node 0 is the root, the
+// other nodes are NOT in breadth-first order then (chunk-local subtrees are contiguous, the top tree's nodes come last).
 // sah_node_cost: cost of one wide-node child box relative to one triangle test in the SAH leaf decision (option "sah_node").
 cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, int n, int max_leaf, int key_bits, float sah_node_cost, BvhResult& out,
                       Arena& ws, cudaStream_t st, float4* tri_rec = nullptr, float2* uvs = nullptr, cudaEvent_t done = nullptr,
-                      void* deferred_counters = nullptr);
+                      void* deferred_counters = nullptr, int build_fused = 1);
 // Asynchronous form: with `deferred_counters` (pinned host memory of build_counters_bytes()) build_bvh does not synchronise; the
 // counters are copied there on the stream BEFORE `done` is recorded, and build_bvh_finish() turns them into out.num_nodes,
 // depth, bounds ... once the caller has seen `done` complete.

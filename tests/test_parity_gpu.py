@@ -329,46 +329,66 @@ def test_empty_and_degenerate(rtb, oracle):
     s.close()
 
 
+def check_tree(nodes, rec, order, tris, info):
+    """every triangle in exactly one leaf, every node but the root referenced exactly once, child boxes contain what is below
+    them, and the statistics of rtb_mesh_info (leaves, largest leaf, depth) are those of the tree that is actually there"""
+    n = len(tris)
+    assert sorted(order.tolist()) == list(range(n))
+    assert np.array_equal(rec[:, 0, 3].view(np.int32), order.view(np.int32))
+    assert rec[:, 1, :3].tobytes() == tris["v"][order, 0].tobytes() and rec[:, 0, :3].tobytes() == tris["n"][order].tobytes()
+    refs = nodes[:, 6, :].view(np.int32)
+    seen = np.zeros(n, np.int32)
+    child_seen = np.zeros(len(nodes), np.int32)
+    level = np.zeros(len(nodes), np.int32)
+    vmin, vmax = tris["v"].min(axis=1)[order], tris["v"].max(axis=1)[order]
+    leaves, largest = 0, 0
+    todo = [0]
+    while todo:                                                       # from the root: the node order in memory is not assumed
+        ni = todo.pop()
+        for k in range(4):
+            r = int(refs[ni, k])
+            if r == -2147483648:
+                continue
+            lo = nodes[ni, [0, 2, 4], k]
+            hi = nodes[ni, [1, 3, 5], k]
+            if r < 0:
+                bits = ~r
+                first, cnt = bits >> 3, (bits & 7) + 1
+                seen[first:first + cnt] += 1
+                leaves, largest = leaves + 1, max(largest, cnt)
+                assert np.all(vmin[first:first + cnt] >= lo) and np.all(vmax[first:first + cnt] <= hi)
+            else:
+                assert 0 < r < len(nodes)
+                child_seen[r] += 1
+                level[r] = level[ni] + 1
+                todo.append(r)
+                clo = nodes[r][[0, 2, 4], :].min(axis=1)
+                chi = np.where(np.isinf(nodes[r][[1, 3, 5], :]), -np.inf, nodes[r][[1, 3, 5], :]).max(axis=1)
+                assert np.all(clo >= lo) and np.all(chi <= hi)
+    assert np.all(seen == 1) and np.all(child_seen[1:] == 1) and child_seen[0] == 0
+    assert info["num_leaves"] == leaves and info["max_leaf_size"] == largest and largest <= 8
+    assert info["depth"] == int(level.max()) + 1 and info["depth"] * 3 + 2 <= 64
+
+
 def test_bvh_invariants_and_wide_keys(rtb):
-    """Builder invariants on both key widths: every triangle in exactly one leaf, child boxes contain their triangles."""
-    tris = synth.bumpy_sphere(40, 80, ground=True)
-    for key_bits in (32, 64):
-        s = rtb.Scene(0)
-        s.set_option("key_bits", key_bits)
-        s.add_material(rtb.Material())
-        s.add_mesh(rtb.MeshPrimitive(tris))
-        s.add_mesh_instance(rtb.MeshInstance(0, 0))
-        s.upload_to_device()
-        nodes, rec, order = s.mesh_arrays(0)
-        info = s.mesh_info(0)
-        s.close()
-        n = len(tris)
-        assert sorted(order.tolist()) == list(range(n))
-        assert np.array_equal(rec[:, 0, 3].view(np.int32), order.view(np.int32))
-        assert rec[:, 1, :3].tobytes() == tris["v"][order, 0].tobytes() and rec[:, 0, :3].tobytes() == tris["n"][order].tobytes()
-        refs = nodes[:, 6, :].view(np.int32)
-        seen = np.zeros(n, np.int32)
-        child_seen = np.zeros(len(nodes), np.int32)
-        vmin, vmax = tris["v"].min(axis=1)[order], tris["v"].max(axis=1)[order]
-        for ni in range(len(nodes)):
-            for k in range(4):
-                r = int(refs[ni, k])
-                if r == -2147483648:
-                    continue
-                lo = nodes[ni, [0, 2, 4], k]
-                hi = nodes[ni, [1, 3, 5], k]
-                if r < 0:
-                    bits = ~r
-                    first, cnt = bits >> 3, (bits & 7) + 1
-                    seen[first:first + cnt] += 1
-                    assert np.all(vmin[first:first + cnt] >= lo) and np.all(vmax[first:first + cnt] <= hi)
-                else:
-                    child_seen[r] += 1
-                    clo = nodes[r][[0, 2, 4], :].min(axis=1)
-                    chi = np.where(np.isinf(nodes[r][[1, 3, 5], :]), -np.inf, nodes[r][[1, 3, 5], :]).max(axis=1)
-                    assert np.all(clo >= lo) and np.all(chi <= hi)
-        assert np.all(seen == 1) and np.all(child_seen[1:] == 1) and child_seen[0] == 0
-        assert info["num_leaves"] > 0 and info["max_leaf_size"] <= 8 and info["depth"] * 3 + 2 <= 64
+    """Builder invariants on both key widths and both collapse forms (one pass over the whole tree; fused with the fit below the
+    256-leaf chunks): a sphere, a larger one, and a mesh of a few distinct triangles repeated many times (equal Morton keys:
+    the tree below is ordered by index only and as deep as it gets)."""
+    few = synth.bumpy_sphere(3, 6)
+    cases = [synth.bumpy_sphere(40, 80, ground=True), synth.bumpy_sphere(90, 180, ground=True), np.concatenate([few] * 150)]
+    for tris in cases:
+        for key_bits, fused in ((32, 1), (64, 1), (32, 0), (64, 0)):
+            s = rtb.Scene(0)
+            s.set_option("key_bits", key_bits)
+            s.set_option("build_fused", fused)
+            s.add_material(rtb.Material())
+            s.add_mesh(rtb.MeshPrimitive(tris))
+            s.add_mesh_instance(rtb.MeshInstance(0, 0))
+            s.upload_to_device()
+            nodes, rec, order = s.mesh_arrays(0)
+            info = s.mesh_info(0)
+            s.close()
+            check_tree(nodes, rec, order, tris, info)
 
 
 def test_instance_update_and_mesh_rebuild(rtb, oracle):

@@ -15,6 +15,8 @@ rep = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 tris = synth.bumpy_sphere(N, M)
 t = torch.from_numpy(tris.view(np.uint8).reshape(-1, 72)).cuda()
 scene = api.Scene(0)
+if os.environ.get("RTB_BUILD_FUSED"):                       # A/B the fused fit + chunk-local collapse against the one-pass collapse
+    scene.set_option("build_fused", int(os.environ["RTB_BUILD_FUSED"]))
 scene.add_material(api.Material())
 mesh = api.MeshPrimitive(tris[:0])
 mesh.device_ptr, mesh.num_triangles = t.data_ptr(), len(tris)
@@ -26,5 +28,6 @@ for i in range(rep):
     t0 = time.perf_counter()
     scene.rebuild_mesh(0, device_ptr=t.data_ptr(), n=len(tris))
     torch.cuda.synchronize()
-    print("rebuild %d: wall %.2f ms, info build_ms %.2f, nodes %d" % (i, 1e3 * (time.perf_counter() - t0), scene.mesh_info(0)["build_ms"], scene.mesh_info(0)["num_nodes"]), flush=True)
+    info = scene.mesh_info(0)
+    print("rebuild %d: wall %.2f ms, info build_ms %.2f, nodes %d leaves %d depth %d" % (i, 1e3 * (time.perf_counter() - t0), info["build_ms"], info["num_nodes"], info["num_leaves"], info["depth"]), flush=True)
 scene.close()
