@@ -264,6 +264,9 @@ def main():
     # ---- scene (replicated on every rank) -------------------------------------------------------
     tris = build_tris(cfg)
     scene = api.Scene(local_rank)
+    for kv in os.environ.get("RTB_OPTIONS", "").split(","):                      # experiments only: "key_bits=32,build_fused=0"
+        if "=" in kv:
+            scene.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     for m in scene_materials(cfg):
         scene.add_material(api.Material(albedo=m["albedo"], metallic=m["metallic"]))
     tris_t = torch.from_numpy(tris.view(np.uint8).reshape(-1, 72)).to(dev)      # triangles resident in HBM

@@ -155,8 +155,10 @@ __global__ void k_morton(const float4* __restrict__ bmin, const float4* __restri
     float ex = ord2f(c->cbounds[3]) - lx, ey = ord2f(c->cbounds[4]) - ly, ez = ord2f(c->cbounds[5]) - lz;
     float nx = ex > 0.f ? (cx - lx) / ex : 0.f, ny = ey > 0.f ? (cy - ly) / ey : 0.f, nz = ez > 0.f ? (cz - lz) / ez : 0.f;
     if (sizeof(K) == 4) {
-        unsigned ix = min(1023u, (unsigned)(nx * 1024.f)), iy = min(1023u, (unsigned)(ny * 1024.f)), iz = min(1023u, (unsigned)(nz * 1024.f));
-        keys[i] = (K)((expand10(ix) << 2) | (expand10(iy) << 1) | expand10(iz));
+        // all 32 bits: 11 bits per axis interleaved, the last z bit dropped (x and y keep 2048 cells, z 1024) -- still a prefix of
+        // the Morton code, so the order is a Morton order; four radix passes over 4-byte keys
+        unsigned long long ix = min(2047u, (unsigned)(nx * 2048.f)), iy = min(2047u, (unsigned)(ny * 2048.f)), iz = min(2047u, (unsigned)(nz * 2048.f));
+        keys[i] = (K)(((expand21(ix) << 2) | (expand21(iy) << 1) | expand21(iz)) >> 1);
     } else {
         // 13 bits per axis = 39-bit keys: FIVE 8-bit radix passes (48-bit keys took six, +117 us per 10 M keys); 8192 cells per axis
         // are still finer than the primitives of any mesh that fits the device (2^39 cells for <= 2^31 primitives), and equal
@@ -535,7 +537,7 @@ __global__ void __launch_bounds__(256) k_fit_top(const int* __restrict__ top_lis
 // the second arrival fits the parent and climbs on.  No node above the chunks is emitted as one leaf (see k_fit_collapse).
 // The thread that completes [0, n - 1] has the root: it seeds the collapse queue with it.
 template <typename K>
-__global__ void __launch_bounds__(256) k_fit_top_fused(const K* __restrict__ keys, const int4* __restrict__ top_list, BuildCounters* c, int n,
+__global__ void __launch_bounds__(64) k_fit_top_fused(const K* __restrict__ keys, const int4* __restrict__ top_list, BuildCounters* c, int n,
                           int* left, int* right, int2* range, float4* nb_min, float4* nb_max, int* visit,
                           int4* __restrict__ topo, float c_node, int2* __restrict__ q0)
 {
@@ -801,7 +803,11 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
         CK(cudaFuncSetAttribute(k_fit_collapse<K>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         k_fit_collapse<K><<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(keys[cur], bmin, bmax, out.order, n, range, nb_min, nb_max, topo, max_leaf,
                                                                                    sah_node_cost, 1.0f, top_list, out.nodes, ctr);
-        k_fit_top_fused<K><<<148 * 4, 256, 0, st>>>(keys[cur], top_list, ctr, n, left, right, range, nb_min, nb_max, visit, topo, sah_node_cost, q0);
+        // one thread per work item where possible (their number is only known on the device; n / 8 threads cover every mesh seen so
+        // far, the loop in the kernel covers the rest): a thread that still has a second item to start after a long climb keeps
+        // everybody who needs that item's subtree waiting.  Small CTAs, so that the slots of finished climbers are reused early.
+        const int top_blocks = std::max(148 * 16, std::min((n / 8 + 63) / 64, 148 * 256));
+        k_fit_top_fused<K><<<top_blocks, 64, 0, st>>>(keys[cur], top_list, ctr, n, left, right, range, nb_min, nb_max, visit, topo, sah_node_cost, q0);
     } else {
         k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
         k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, sah_node_cost, 1.0f,

@@ -31,7 +31,9 @@ constexpr int NODE_F4 = 7;
 constexpr int TRI_F4 = 4;           // float4 per triangle record
 constexpr int INST_F4 = 6;          // float4 per instance record
 constexpr int MAX_LEAF = 8;         // triangles per leaf (3-bit count)
-constexpr int STACK_CAP = 64;       // traversal stack entries per ray
+constexpr int STACK_CAP = 96;       // traversal stack entries per ray: worst case 3 per tree level (rtb_api.cu make_scene refuses deeper scenes).
+                                    // Per-thread local memory: only the entries a ray reaches are ever touched, so the size costs nothing;
+                                    // 64 refused C3 once the 1 M-triangle BLAS came out 16 levels deep (3 * 5 + 1 + 3 * 16 + 2 = 66)
 constexpr int EMPTY_REF = (int)0x80000000;   // child slot without a subtree
 constexpr int BAND_ROWS = 8;        // image rows per multi-GPU band
 

@@ -367,7 +367,7 @@ def check_tree(nodes, rec, order, tris, info):
                 assert np.all(clo >= lo) and np.all(chi <= hi)
     assert np.all(seen == 1) and np.all(child_seen[1:] == 1) and child_seen[0] == 0
     assert info["num_leaves"] == leaves and info["max_leaf_size"] == largest and largest <= 8
-    assert info["depth"] == int(level.max()) + 1 and info["depth"] * 3 + 2 <= 64
+    assert info["depth"] == int(level.max()) + 1 and info["depth"] * 3 + 2 <= 96
 
 
 def test_bvh_invariants_and_wide_keys(rtb):

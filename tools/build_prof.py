@@ -17,6 +17,9 @@ t = torch.from_numpy(tris.view(np.uint8).reshape(-1, 72)).cuda()
 scene = api.Scene(0)
 if os.environ.get("RTB_BUILD_FUSED"):                       # A/B the fused fit + chunk-local collapse against the one-pass collapse
     scene.set_option("build_fused", int(os.environ["RTB_BUILD_FUSED"]))
+for kv in os.environ.get("RTB_OPTIONS", "").split(","):
+    if "=" in kv:
+        scene.set_option(kv.split("=")[0], int(kv.split("=")[1]))
 scene.add_material(api.Material())
 mesh = api.MeshPrimitive(tris[:0])
 mesh.device_ptr, mesh.num_triangles = t.data_ptr(), len(tris)
