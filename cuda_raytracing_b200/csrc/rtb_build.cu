@@ -2,10 +2,13 @@
 //
 // Replaces the reference's single-threaded recursive host builder (BVHTree::fill, BVHTree.hpp:203-292,
 // 15 re-scans per node) and its one-cudaMalloc-per-leaf upload (BVHTree.hpp:97-114,364-383):
-//   prim boxes -> scene bounds -> Morton keys -> radix sort -> Karras 2012 radix tree -> bottom-up
-//   AABB fit + SAH leaf decision -> top-down collapse to 128-byte BVH4 nodes -> triangle records.
-// The tree only culls (rtb_trace.cuh keeps the reference's hit predicate), so it is free to differ
-// from the reference's tree.  All stages are HBM-bound streaming kernels.
+//   prim boxes -> scene bounds -> Morton keys -> radix sort -> radix tree + AABB fit + SAH leaf decision -> collapse to 112-byte
+//   BVH4 nodes -> triangle records.
+// Meshes of >= FUSED_MIN_PRIMS primitives take the fused form: k_fit_collapse does tree, fit and collapse of everything below
+// the 256-leaf chunks of the sorted order in shared memory, k_fit_top_fused + k_collapse finish the few nodes above them.
+// Smaller meshes and the TLAS take the one-pass form: k_hierarchy (Karras 2012), k_fit + k_fit_top, k_collapse over the whole tree.
+// The tree only culls (rtb_trace.cuh keeps the reference's hit predicate), so it is free to differ from the reference's tree.
+// Streaming stages run near the HBM peak; the tree stages are latency chains (DESIGN.md 4 has the launch list).
 #include "rtb_build.cuh"
 #include "rtb_sort.cuh"
 #include <cstdio>
