@@ -29,6 +29,10 @@ void Arena::release()
 {
     if (base) cudaFree(base);
     base = nullptr; cap = used = 0;
+    if (side) cudaStreamDestroy(side);
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    if (ev_join) cudaEventDestroy(ev_join);
+    side = nullptr; ev_fork = ev_join = nullptr;
 }
 
 // ------------------------------------------------------------------ helpers
@@ -775,9 +779,16 @@ __global__ void k_emit_tris(const rtb_triangle* __restrict__ tris, int n, const 
 // ------------------------------------------------------------------ host side
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 
+static cudaError_t emit_records(const rtb_triangle* tris_dev, int n, const unsigned* order, float4* tri_rec, float2* uvs, cudaStream_t st);
+
+// `fork`: triangle records wanted (tris / tri_rec / uvs set).  In the fused build they are written on the arena's side stream, from
+// the moment k_fit_collapse has been enqueued: k_emit_tris needs the sorted order only, and it streams 1.6 GB while the two kernels
+// that finish the top of the tree are chains of dependent L2 round trips on a handful of warps.  *forked tells the caller to join.
+struct EmitJob { const rtb_triangle* tris; float4* tri_rec; float2* uvs; bool forked; };
+
 template <typename K>
 static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int max_leaf, int key_bits, float sah_node_cost, BvhResult& out,
-                              Arena& ws, BuildCounters* ctr, cudaStream_t st, bool fused)
+                              Arena& ws, BuildCounters* ctr, cudaStream_t st, bool fused, EmitJob* job)
 {
     K* keys[2]; unsigned* vals[2];
     keys[0] = ws.take<K>(n); keys[1] = ws.take<K>(n);
@@ -810,7 +821,22 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
         // far, the loop in the kernel covers the rest): a thread that still has a second item to start after a long climb keeps
         // everybody who needs that item's subtree waiting.  Small CTAs, so that the slots of finished climbers are reused early.
         const int top_blocks = std::max(148 * 16, std::min((n / 8 + 63) / 64, 148 * 256));
+        const bool fork = job && job->tris;
+        if (fork) {
+            if (!ws.side) {
+                CK(cudaStreamCreateWithFlags(&ws.side, cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&ws.ev_fork, cudaEventDisableTiming));
+                CK(cudaEventCreateWithFlags(&ws.ev_join, cudaEventDisableTiming));
+            }
+            CK(cudaEventRecord(ws.ev_fork, st));                        // = k_fit_collapse done (the event must not cover the top fit)
+        }
         k_fit_top_fused<K><<<top_blocks, 64, 0, st>>>(keys[cur], top_list, ctr, n, left, right, range, nb_min, nb_max, visit, topo, sah_node_cost, q0);
+        if (fork) {                                                     // enqueued after the top fit, so its few climbers get their slots first
+            CK(cudaStreamWaitEvent(ws.side, ws.ev_fork, 0));
+            CK(emit_records(job->tris, n, out.order, job->tri_rec, job->uvs, ws.side));
+            CK(cudaEventRecord(ws.ev_join, ws.side));
+            job->forked = true;
+        }
     } else {
         k_hierarchy<K><<<g, 256, 0, st>>>(keys[cur], n, left, right, parent, range);
         k_fit<<<(n + FIT_CHUNK - 1) / FIT_CHUNK, FIT_CHUNK, 0, st>>>(bmin, bmax, out.order, n, left, right, parent, range, nb_min, nb_max, visit, topo, max_leaf, sah_node_cost, 1.0f,
@@ -835,6 +861,13 @@ static cudaError_t build_tree(const float4* bmin, const float4* bmax, int n, int
     float4* nodes_out = out.nodes;
     void* args[] = { &q0, &q1, &n, &left, &right, &range, &nb_min, &nb_max, &topo, &nodes_out, &ctr };
     CK(cudaLaunchCooperativeKernel((const void*)k_collapse, dim3(std::min(resident, (n + 127) / 128)), dim3(128), args, 0, st));
+    return cudaGetLastError();
+}
+
+static cudaError_t emit_records(const rtb_triangle* tris_dev, int n, const unsigned* order, float4* tri_rec, float2* uvs, cudaStream_t st)
+{
+    if (((uintptr_t)tris_dev & 7u) == 0) k_emit_tris<true><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, order, tri_rec, uvs);
+    else k_emit_tris<false><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, order, tri_rec, uvs);
     return cudaGetLastError();
 }
 
@@ -883,6 +916,7 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
     CK(ws.reserve(bytes));
     ws.reset();
     BuildCounters* ctr = ws.take<BuildCounters>(1);
+    EmitJob job = { (tris_dev && tri_rec && uvs && n > 0) ? tris_dev : nullptr, tri_rec, uvs, false };
     k_init_counters<<<1, 96, 0, st>>>(ctr);
     if (n > 0) {
         const int gb = (n + 256 * BB_PER - 1) / (256 * BB_PER);
@@ -893,16 +927,14 @@ cudaError_t build_bvh(const rtb_triangle* tris_dev, float4* bmin, float4* bmax, 
         k_trivial_root<<<1, 1, 0, st>>>(out.nodes, bmin, bmax, n);
         if (n == 1) k_iota<<<1, 32, 0, st>>>(out.order, 1);
     } else if (wide_keys) {
-        CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 40, sah_node_cost, out, ws, ctr, st, fused));
+        CK(build_tree<unsigned long long>(bmin, bmax, n, max_leaf, 40, sah_node_cost, out, ws, ctr, st, fused, &job));
     } else {
-        CK(build_tree<unsigned>(bmin, bmax, n, max_leaf, 32, sah_node_cost, out, ws, ctr, st, fused));
+        CK(build_tree<unsigned>(bmin, bmax, n, max_leaf, 32, sah_node_cost, out, ws, ctr, st, fused, &job));
     }
     // triangle records in leaf order: enqueued BEFORE the counters are read back, so the device does not idle while the host
     // wakes up from the synchronisation below (one host round trip per build instead of two)
-    if (tris_dev && tri_rec && uvs && n > 0) {
-        if (((uintptr_t)tris_dev & 7u) == 0) k_emit_tris<true><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, out.order, tri_rec, uvs);
-        else k_emit_tris<false><<<(n + 255) / 256, 256, 0, st>>>(tris_dev, n, out.order, tri_rec, uvs);
-    }
+    if (job.forked) CK(cudaStreamWaitEvent(st, ws.ev_join, 0));        // the records were written on the side stream: join before anything that follows
+    else if (tris_dev && tri_rec && uvs && n > 0) CK(emit_records(tris_dev, n, out.order, tri_rec, uvs, st));
     if (deferred_counters) {
         // asynchronous build: the counters travel to pinned host memory on the stream, `done` is recorded after them and the
         // caller reads them with build_bvh_finish() once that event has completed -- no host synchronisation here

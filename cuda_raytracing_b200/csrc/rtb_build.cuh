@@ -18,6 +18,10 @@ struct Arena {
     }
     void reset() { used = 0; }
     void release();
+    // A second stream of the builder that owns this arena (created on first use, destroyed by release()): the triangle records are
+    // written there while the latency-bound top of the tree is made on the caller's stream (rtb_build.cu build_bvh).
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 struct BvhResult {
