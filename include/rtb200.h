@@ -120,7 +120,8 @@ RTB_API int rtb_mesh_commit(rtb_context* ctx, int mesh_id);
 RTB_API int rtb_mesh_info_get(rtb_context* ctx, int mesh_id, rtb_mesh_info* out);
 RTB_API int rtb_mesh_destroy(rtb_context* ctx, int mesh_id);
 /* Inspection (tools/tests; the analogue of BVHTree::print_stats, BVHTree.hpp:117-172): copies device arrays to the host.
- * what = 0: wide nodes (num_nodes * 112 B), 1: triangle records (num_triangles * 64 B), 2: leaf order (num_triangles * 4 B) */
+ * what = 0: wide nodes (num_nodes * 112 B; node 0 is the root, the order of the others is the builder's business), 1: triangle
+ * records (num_triangles * 64 B), 2: leaf order (num_triangles * 4 B) */
 RTB_API int rtb_mesh_read(rtb_context* ctx, int mesh_id, int what, void* out, size_t bytes);
 
 /* ---- scene: replaces Scene::upload_to_device (Scene.cpp:25-65) / update_mesh_instance (67-74),
